@@ -1,0 +1,224 @@
+// Build-time operations on the host scene model (see scene.hpp for the reference map).
+#include "scene.hpp"
+
+#include <atomic>
+
+namespace rtc {
+
+size_t Shape::next_id() {  // shape.zig:122-131 : process-wide counter
+    static std::atomic<size_t> counter{0};
+    return counter.fetch_add(1);
+}
+
+// ---- BBox ----------------------------------------------------------------------------------------
+BBox BBox::transform(const Mat4& m) const {
+    // Corner order as in bounding_box.zig:50-57.  Infinite extents meet zero matrix entries as
+    // inf*0 = NaN, and add() (fmin/fmax) then ignores that corner -- the reference quirk that can
+    // leave the box "empty" (min=+inf,max=-inf), which its slab test always passes.
+    const Tuple c[8] = {min,
+                        Tuple::point(min.x, min.y, max.z),
+                        Tuple::point(min.x, max.y, min.z),
+                        Tuple::point(min.x, max.y, max.z),
+                        Tuple::point(max.x, min.y, min.z),
+                        Tuple::point(max.x, min.y, max.z),
+                        Tuple::point(max.x, max.y, min.z),
+                        max};
+    BBox out;
+    for (const Tuple& p : c) out.add(m.tuple_mul(p));
+    return out;
+}
+
+void BBox::split(BBox& left, BBox& right) const {
+    double dx = max.x - min.x, dy = max.y - min.y, dz = max.z - min.z;
+    double greatest = std::fmax(dx, std::fmax(dy, dz));
+    double x0 = min.x, y0 = min.y, z0 = min.z, x1 = max.x, y1 = max.y, z1 = max.z;
+    if (greatest == dx) {
+        x0 = x0 + dx / 2.0;
+        x1 = x0;
+    } else if (greatest == dy) {
+        y0 = y0 + dy / 2.0;
+        y1 = y0;
+    } else {
+        z0 = z0 + dz / 2.0;
+        z1 = z0;
+    }
+    left.min = min;
+    left.max = Tuple::point(x1, y1, z1);
+    right.min = Tuple::point(x0, y0, z0);
+    right.max = max;
+}
+
+// ---- Shape construction --------------------------------------------------------------------------
+Shape Shape::triangle(const Tuple& p1, const Tuple& p2, const Tuple& p3) {  // shape.zig:186-206
+    Shape s = make(ShapeKind::Triangle);
+    s.p1 = p1;
+    s.p2 = p2;
+    s.p3 = p3;
+    s.e1 = p2.sub(p1);
+    s.e2 = p3.sub(p1);
+    s.normal = s.e2.cross(s.e1).normalized();
+    return s;
+}
+
+Shape Shape::smooth_triangle(const Tuple& p1, const Tuple& p2, const Tuple& p3, const Tuple& n1,
+                             const Tuple& n2, const Tuple& n3) {  // shape.zig:208-229
+    Shape s = make(ShapeKind::SmoothTriangle);
+    s.p1 = p1;
+    s.p2 = p2;
+    s.p3 = p3;
+    s.e1 = p2.sub(p1);
+    s.e2 = p3.sub(p1);
+    s.n1 = n1;
+    s.n2 = n2;
+    s.n3 = n3;
+    return s;
+}
+
+Shape Shape::group() {  // shape.zig:237-252 : the bbox is itself a Shape there and takes an id
+    (void)next_id();
+    return make(ShapeKind::Group);
+}
+
+Shape Shape::csg(CsgOp op, Shape left, Shape right) {  // shape.zig:254-281
+    BBox box = left.parent_space_bounds();
+    box.merge(right.parent_space_bounds());
+    Shape s = make(ShapeKind::Csg);
+    s.bbox = box;
+    s.op = op;
+    s.left = std::shared_ptr<Shape>(new Shape(std::move(left)));
+    s.right = std::shared_ptr<Shape>(new Shape(std::move(right)));
+    return s;
+}
+
+void Shape::set_transform(const Mat4& m) {
+    switch (kind) {
+        case ShapeKind::Group:
+            for (Shape& c : children) c.set_transform(m.mul(c.transform));
+            bbox = bbox.transform(m);
+            break;
+        case ShapeKind::Csg:
+            // NB: `_bbox` is NOT updated here in the reference (shape.zig:298-302).
+            left->set_transform(m.mul(left->transform));
+            right->set_transform(m.mul(right->transform));
+            break;
+        default:
+            transform = m;
+            inverse = m.inverse();
+            inverse_transpose = inverse.transpose();
+    }
+}
+
+BBox Shape::bounds() const {
+    BBox b;
+    switch (kind) {
+        case ShapeKind::Test:
+        case ShapeKind::Sphere:
+        case ShapeKind::Cube:
+            b.min = Tuple::point(-1, -1, -1);
+            b.max = Tuple::point(1, 1, 1);
+            break;
+        case ShapeKind::Plane:  // plane.zig:45-53
+            b.min = Tuple::point(-kInf, 0, -kInf);
+            b.max = Tuple::point(kInf, 0, kInf);
+            break;
+        case ShapeKind::Cylinder:  // cylinder.zig:114-120
+            b.min = Tuple::point(-1, minimum, -1);
+            b.max = Tuple::point(1, maximum, 1);
+            break;
+        case ShapeKind::Cone: {  // cone.zig:129-137
+            double limit = std::fmax(std::fabs(minimum), std::fabs(maximum));
+            b.min = Tuple::point(-limit, minimum, -limit);
+            b.max = Tuple::point(limit, maximum, limit);
+            break;
+        }
+        case ShapeKind::Triangle:
+        case ShapeKind::SmoothTriangle:
+            b.add(p1);
+            b.add(p2);
+            b.add(p3);
+            break;
+        case ShapeKind::Group:
+        case ShapeKind::Csg:
+            b = bbox;
+            break;
+    }
+    return b;
+}
+
+void Shape::add_child(Shape child) {
+    bbox.merge(child.parent_space_bounds());
+    children.push_back(std::move(child));
+}
+
+void Shape::partition_children(std::vector<Shape>& left, std::vector<Shape>& right) {
+    BBox lb, rb;
+    bbox.split(lb, rb);
+    std::vector<Shape> keep;
+    for (Shape& c : children) {
+        BBox cb = c.parent_space_bounds();
+        if (lb.contains_box(cb))
+            left.push_back(std::move(c));
+        else if (rb.contains_box(cb))
+            right.push_back(std::move(c));
+        else
+            keep.push_back(std::move(c));
+    }
+    children = std::move(keep);
+}
+
+void Shape::make_subgroup(std::vector<Shape>& members) {
+    Shape sub = Shape::group();
+    for (Shape& m : members) sub.add_child(std::move(m));
+    add_child(std::move(sub));
+}
+
+void Shape::divide(size_t threshold) {
+    if (kind == ShapeKind::Group) {
+        if (children.size() >= threshold) {
+            std::vector<Shape> l, r;
+            partition_children(l, r);
+            if (!l.empty()) make_subgroup(l);
+            if (!r.empty()) make_subgroup(r);
+        }
+        for (Shape& c : children) c.divide(threshold);
+    } else if (kind == ShapeKind::Csg) {
+        left->divide(threshold);
+        right->divide(threshold);
+    }
+}
+
+// ---- World / Camera ------------------------------------------------------------------------------
+World World::default_world() {
+    World w;
+    Shape s1 = Shape::sphere();
+    Material m;
+    m.pattern = share(Pattern::solid({0.8, 1.0, 0.6}));
+    m.diffuse = 0.7;
+    m.specular = 0.2;
+    s1.material = m;
+    Shape s2 = Shape::sphere();
+    s2.set_transform(Mat4::identity().scale(0.5, 0.5, 0.5));
+    w.objects.push_back(std::move(s1));
+    w.objects.push_back(std::move(s2));
+    w.lights.push_back({Tuple::point(-10, 10, -10), {1, 1, 1}});
+    return w;
+}
+
+Camera Camera::make(size_t hsize, size_t vsize, double fov) {
+    Camera c;
+    double half_view = std::tan(fov / 2.0);
+    double aspect = (double)hsize / (double)vsize;
+    c.half_width = half_view * aspect;
+    c.half_height = half_view;
+    if (aspect >= 1.0) {
+        c.half_width = half_view;
+        c.half_height = half_view / aspect;
+    }
+    c.hsize = hsize;
+    c.vsize = vsize;
+    c.fov = fov;
+    c.pixel_size = (c.half_width * 2.0) / (double)hsize;
+    return c;
+}
+
+}  // namespace rtc
