@@ -1,0 +1,23 @@
+# Builds the product library (sm_100a only) and, through oracle/Makefile, the test oracle.
+PKG := ray-tracer-challenge_b200
+CSRC := $(PKG)/csrc
+NVCC ?= nvcc
+NVFLAGS ?= -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-Wall
+SRC := $(CSRC)/render.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
+       $(CSRC)/host/scene.cpp $(CSRC)/host/scene_parser.cpp $(CSRC)/host/obj.cpp $(CSRC)/host/images.cpp \
+       $(CSRC)/host/flatten.cpp
+HDR := $(wildcard $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh $(CSRC)/host/*.hpp include/*.h)
+
+all: $(PKG)/librtc_b200.so oracle
+
+$(PKG)/librtc_b200.so: $(SRC) $(HDR)
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(SRC) -lz
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -f $(PKG)/librtc_b200.so
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

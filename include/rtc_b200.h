@@ -1,0 +1,90 @@
+/* rtc_b200.h — C ABI of the B200 renderer that replaces the reference's CPU render loop.
+ *
+ * Replaces:  Camera(T).render(self, allocator, world) !Canvas(T)      src/raytracer/camera.zig:80-125
+ *            Renderer.startRender / renderWorker (RGBA8 twin)          src/lib.zig:135-164
+ * and everything those call per pixel (World.colorAt, world.zig:111).  Plain pointers and sizes
+ * only; no allocator, no Zig or torch type crosses this boundary.  Every function returns 0 on
+ * success or a negative rtc_status; rtc_last_error() gives the message for the calling thread.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with
+ * RTC_ERR_CUDA.
+ */
+#ifndef RTC_B200_H
+#define RTC_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#include "rtc_blob.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum rtc_status {
+    RTC_OK = 0,
+    RTC_ERR_INVALID = -1,  /* bad argument / malformed blob */
+    RTC_ERR_CUDA = -2,     /* no device, launch or copy failure */
+    RTC_ERR_PARSE = -3,    /* scene JSON / OBJ / image error (host loader) */
+    RTC_ERR_CAPACITY = -4  /* a per-ray CSG interval list or traversal stack overflowed */
+} rtc_status;
+
+typedef struct rtc_scene rtc_scene; /* device-resident scene, opaque */
+
+/* Camera(T) fields read by rayForPixel (camera.zig:22-30, :64-76). */
+typedef struct rtc_camera {
+    uint64_t hsize, vsize;
+    double half_width, half_height, pixel_size;
+    double inverse[16]; /* Camera._inverse_transform, row-major */
+} rtc_camera;
+
+/* Which rows of the frame this call renders: interleaved scanline tiles.  Row y belongs to the
+ * call iff (y / tile_rows) % n_parts == part.  {1,0,1} = whole frame. */
+typedef struct rtc_partition {
+    uint32_t tile_rows, part, n_parts;
+} rtc_partition;
+
+typedef struct rtc_stats {
+    uint64_t primary_rays, shadow_rays, secondary_rays; /* world.zig:91-92,160-165,178-187 */
+    uint64_t pixels;
+    float kernel_ms; /* CUDA-event time of the render kernel(s) of this call */
+    float pad;
+    uint64_t launches; /* kernels launched by this call */
+} rtc_stats;
+
+const char* rtc_last_error(void);
+int rtc_device_count(void);
+/* Selects the CUDA device used by scenes created afterwards on this thread (default 0). */
+int rtc_set_device(int device);
+
+/* Scene lifetime.  The blob is copied; the caller may free it as soon as the call returns. */
+int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out);
+void rtc_scene_destroy(rtc_scene* scene);
+
+/* camera.zig:80 twin.  rgb_out: caller-owned HOST memory, hsize*vsize*3 doubles, row-major, y down,
+ * linear RGB exactly as Canvas.pixels holds it.  Rows outside `part` (NULL = whole frame) are left
+ * untouched.  max_depth is the `remaining_recursions` seed (5 at camera.zig:118). */
+int rtc_render(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+               double* rgb_out, rtc_stats* stats);
+/* lib.zig:135-155 twin: clamp()-quantised RGBA8 (color.zig:61-71), alpha 255, 4 bytes per pixel. */
+int rtc_render_rgba8(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+                     uint8_t* rgba_out, rtc_stats* stats);
+/* Same render, result left in DEVICE memory owned by the caller (e.g. a torch tensor used as an
+ * NCCL send buffer): d_rgb holds the rows of `part` only, packed in increasing y,
+ * rtc_partition_rows(...) * hsize * 3 doubles.  `stream` is a cudaStream_t (NULL = default). */
+int rtc_render_device(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+                      double* d_rgb, void* stream, rtc_stats* stats);
+uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part);
+
+/* Host loader: the C++ mirror of src/parsing (scene.zig:612, obj.zig:195) + flattener, for hosts
+ * that do not have the Zig parsing layer at hand (tests, bench, Python).  width/height > 0 replace
+ * camera.width/height (the reference's only resolution knob, scene.zig:629-631).
+ * rtc_blob_free releases the buffer. */
+int rtc_load_scene_json(const char* json_text, const char* asset_dir, long width, long height,
+                        void** blob_out, size_t* nbytes_out, rtc_camera* cam_out);
+void rtc_blob_free(void* blob);
+/* lib.zig:166-190 camera orbit: rebuilds cam->inverse from from/to/up (matrix.zig:54-67). */
+int rtc_camera_look_at(rtc_camera* cam, const double from[3], const double to[3], const double up[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

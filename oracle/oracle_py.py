@@ -13,7 +13,7 @@ _LIB = None
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    if force or not os.path.exists(so) or not os.path.exists(os.path.join(_HERE, "kat_tests")):
+    if force or not os.path.exists(so):
         subprocess.check_call(["make", "-C", _HERE, "all"], stdout=subprocess.DEVNULL)
     return so
 

@@ -1,0 +1,234 @@
+"""B200-native renderer for the per-pixel hot path of SinclaM/ray-tracer-challenge.
+
+Host-side mirror of the reference's operator interface for this path:
+
+    info   = parse_scene(json_text, asset_dir)         # src/parsing/scene.zig:612  parseScene
+    canvas = info.camera.render(info.world)            # src/raytracer/camera.zig:80 Camera.render
+    canvas.pixels          # [H, W, 3] float64 linear RGB, row-major, y down (canvas.zig:18-21)
+    canvas.to_image()      # [H, W, 3] uint8, clamp() quantised       (canvas.zig:150-176)
+
+Everything is a thin ctypes layer over the C ABI in include/rtc_b200.h (librtc_b200.so, built
+in-tree by `make` / __graft_entry__.build()).  There is no CPU fallback: importing works anywhere,
+but creating a World needs the library and a CUDA device, and fails loudly otherwise.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtc_b200.so")
+_lib = None
+
+RTC_OK, RTC_ERR_INVALID, RTC_ERR_CUDA, RTC_ERR_PARSE, RTC_ERR_CAPACITY = 0, -1, -2, -3, -4
+
+
+class RtcError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("rtc_b200 error %d: %s" % (code, message))
+        self.code = code
+
+
+class rtc_camera(ctypes.Structure):
+    _fields_ = [("hsize", ctypes.c_uint64), ("vsize", ctypes.c_uint64), ("half_width", ctypes.c_double),
+                ("half_height", ctypes.c_double), ("pixel_size", ctypes.c_double), ("inverse", ctypes.c_double * 16)]
+
+
+class rtc_partition(ctypes.Structure):
+    _fields_ = [("tile_rows", ctypes.c_uint32), ("part", ctypes.c_uint32), ("n_parts", ctypes.c_uint32)]
+
+
+class rtc_stats(ctypes.Structure):
+    _fields_ = [("primary_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64),
+                ("secondary_rays", ctypes.c_uint64), ("pixels", ctypes.c_uint64), ("kernel_ms", ctypes.c_float),
+                ("pad", ctypes.c_float), ("launches", ctypes.c_uint64)]
+
+    def as_dict(self):
+        return {"primary": self.primary_rays, "shadow": self.shadow_rays, "secondary": self.secondary_rays,
+                "pixels": self.pixels, "kernel_ms": self.kernel_ms, "launches": self.launches}
+
+    @property
+    def rays(self):
+        return self.primary_rays + self.shadow_rays + self.secondary_rays
+
+
+# every symbol include/rtc_b200.h declares
+EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
+           "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_partition_rows", "rtc_load_scene_json",
+           "rtc_blob_free", "rtc_camera_look_at"]
+
+
+def lib():
+    """Loads librtc_b200.so (no compute happens at load time)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RtcError(RTC_ERR_CUDA, "%s is missing: run `make` (or __graft_entry__.build()); there is no fallback path"
+                       % LIB_PATH)
+    L = ctypes.CDLL(LIB_PATH)
+    vp, cp = ctypes.c_void_p, ctypes.c_char_p
+    L.rtc_last_error.restype = cp
+    L.rtc_device_count.restype = ctypes.c_int
+    L.rtc_set_device.argtypes = [ctypes.c_int]
+    L.rtc_scene_create.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
+    L.rtc_scene_destroy.argtypes = [vp]
+    L.rtc_scene_destroy.restype = None
+    common = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, ctypes.POINTER(rtc_partition)]
+    L.rtc_render.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_render_rgba8.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_render_device.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_partition_rows.argtypes = [ctypes.c_uint64, ctypes.POINTER(rtc_partition)]
+    L.rtc_partition_rows.restype = ctypes.c_uint64
+    L.rtc_load_scene_json.argtypes = [cp, cp, ctypes.c_long, ctypes.c_long, ctypes.POINTER(vp),
+                                      ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(rtc_camera)]
+    L.rtc_blob_free.argtypes = [vp]
+    L.rtc_blob_free.restype = None
+    L.rtc_camera_look_at.argtypes = [ctypes.POINTER(rtc_camera)] + [ctypes.POINTER(ctypes.c_double)] * 3
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise RtcError(rc, lib().rtc_last_error().decode(errors="replace"))
+
+
+def device_count():
+    return lib().rtc_device_count()
+
+
+def load_blob(json_text, asset_dir="", width=0, height=0):
+    """Host loader (C++ mirror of src/parsing): -> (blob bytes, rtc_camera).  Needs no GPU."""
+    L = lib()
+    blob, n, cam = ctypes.c_void_p(), ctypes.c_size_t(), rtc_camera()
+    _check(L.rtc_load_scene_json(json_text.encode(), asset_dir.encode(), width, height, ctypes.byref(blob),
+                                 ctypes.byref(n), ctypes.byref(cam)))
+    try:
+        data = ctypes.string_at(blob, n.value)
+    finally:
+        L.rtc_blob_free(blob)
+    return data, cam
+
+
+class Canvas:
+    """canvas.zig:18-21: width, height, pixels (linear RGB)."""
+
+    def __init__(self, pixels, stats=None):
+        self.pixels = pixels
+        self.height, self.width = pixels.shape[:2]
+        self.stats = stats
+
+    def to_image(self):
+        """Canvas.toImage (canvas.zig:150-176) with color.zig:61-71 clamp(): round-half-away(c*255) in [0,255]."""
+        t = self.pixels * 255.0
+        r = np.where(t >= 0, np.floor(t + 0.5), -np.floor(-t + 0.5))
+        return np.clip(np.nan_to_num(r, nan=0.0), 0, 255).astype(np.uint8)
+
+    def ppm(self):
+        """Canvas.ppm (canvas.zig:181-254) without the 70-column wrapping (plain P3)."""
+        img = self.to_image()
+        rows = [" ".join(str(v) for v in row.reshape(-1)) for row in img]
+        return "P3\n%d %d\n255\n%s\n" % (self.width, self.height, "\n".join(rows))
+
+
+class World:
+    """Device-resident world (world.zig:20-25 after flattening).  Owns the rtc_scene handle."""
+
+    def __init__(self, blob, device=0):
+        L = lib()
+        if L.rtc_device_count() <= 0:
+            raise RtcError(RTC_ERR_CUDA, "no CUDA device visible; this renderer has no CPU fallback")
+        _check(L.rtc_set_device(device))
+        self._h = ctypes.c_void_p()
+        self._blob_bytes = len(blob)
+        _check(L.rtc_scene_create(blob, len(blob), ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rtc_scene_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Camera:
+    """camera.zig:16-125.  render() is the drop-in for Camera.render."""
+
+    def __init__(self, cam):
+        self.c = cam
+
+    @property
+    def hsize(self):
+        return int(self.c.hsize)
+
+    @property
+    def vsize(self):
+        return int(self.c.vsize)
+
+    def look_at(self, frm, to, up):
+        """lib.zig:166-190 (rotateCamera / moveCamera recompute the view from from/to/up)."""
+        a = [(ctypes.c_double * 3)(*v) for v in (frm, to, up)]
+        _check(lib().rtc_camera_look_at(ctypes.byref(self.c), *a))
+
+    @staticmethod
+    def _part(partition):
+        if partition is None:
+            return None, None
+        p = rtc_partition(*partition)
+        return p, ctypes.byref(p)
+
+    def render(self, world, max_depth=5, partition=None, out=None):
+        """-> Canvas.  partition = (tile_rows, part, n_parts) renders only those rows (others stay 0)."""
+        h, w = self.vsize, self.hsize
+        if out is None:
+            out = np.zeros((h, w, 3), dtype=np.float64)
+        assert out.dtype == np.float64 and out.shape == (h, w, 3) and out.flags["C_CONTIGUOUS"]
+        st = rtc_stats()
+        keep, pref = self._part(partition)
+        _check(lib().rtc_render(world._h, ctypes.byref(self.c), max_depth, pref, out.ctypes.data, ctypes.byref(st)))
+        return Canvas(out, st)
+
+    def render_rgba8(self, world, max_depth=5, partition=None):
+        """lib.zig:135-155 twin -> ([H,W,4] uint8, stats)."""
+        h, w = self.vsize, self.hsize
+        out = np.zeros((h, w, 4), dtype=np.uint8)
+        st = rtc_stats()
+        keep, pref = self._part(partition)
+        _check(lib().rtc_render_rgba8(world._h, ctypes.byref(self.c), max_depth, pref, out.ctypes.data,
+                                      ctypes.byref(st)))
+        return out, st
+
+    def partition_rows(self, partition):
+        keep, pref = self._part(partition)
+        return int(lib().rtc_partition_rows(self.vsize, pref))
+
+    def render_device(self, world, d_ptr, max_depth=5, partition=None, stream=0):
+        """Result stays in device memory at d_ptr (packed partition rows, float64 RGB)."""
+        st = rtc_stats()
+        keep, pref = self._part(partition)
+        _check(lib().rtc_render_device(world._h, ctypes.byref(self.c), max_depth, pref, ctypes.c_void_p(d_ptr),
+                                       ctypes.c_void_p(stream), ctypes.byref(st)))
+        return st
+
+
+class SceneInfo:
+    """scene.zig:608-610: { camera, world }."""
+
+    def __init__(self, camera, world):
+        self.camera, self.world = camera, world
+
+
+def parse_scene(json_text, asset_dir="", width=0, height=0, device=0):
+    """parseScene (scene.zig:612-661) + upload.  width/height override camera.width/height."""
+    blob, cam = load_blob(json_text, asset_dir, width, height)
+    return SceneInfo(Camera(cam), World(blob, device))
+
+
+def parse_scene_file(path, asset_dir="", width=0, height=0, device=0):
+    with open(path) as f:
+        return parse_scene(f.read(), asset_dir, width, height, device)

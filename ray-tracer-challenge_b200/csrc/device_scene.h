@@ -1,0 +1,80 @@
+// Device-resident scene: what rtc_scene_create builds out of a blob (include/rtc_blob.h) and what
+// the render kernels read.  Layout rules: every record is a multiple of 16 bytes and is fetched
+// with 16-byte loads (double2 / float4 / int4); arrays are 256-byte aligned cudaMalloc regions of
+// one slab, so one H2D copy uploads a scene.
+#pragma once
+#include <vector_types.h>
+
+#include <cstdint>
+
+#include "../../include/rtc_b200.h"
+
+namespace rtc {
+
+// Triangle record in BVH leaf order, object space, f64 (triangle.zig:22-27).  80 bytes = 5 x 16.
+struct DTri {
+    double p1[3], e1[3], e2[3];
+    int32_t leaf;  // rtc_leaf index: material / normals / tie-break order
+    int32_t pad;
+};
+static_assert(sizeof(DTri) == 80, "DTri must be 80 bytes");
+
+// Two-child BVH node with both child boxes inline, f32 rounded OUTWARD from the f64 triangle
+// bounds.  64 bytes = 4 x float4.  n == 0: child c is an inner node; n > 0: c is the first of n
+// DTri records.  An unused child has an inverted box (lo=+inf, hi=-inf) and n = 0, c = -1.
+struct BvhNode {
+    float lo0[3], hi0[3], lo1[3], hi1[3];
+    int32_t c0, c1, n0, n1;
+};
+static_assert(sizeof(BvhNode) == 64, "BvhNode must be 64 bytes");
+
+// One mesh = all non-CSG triangles sharing a world->object matrix and a casts_shadow flag.
+struct DMesh {
+    int32_t transform;   // rtc_transform index
+    uint32_t flags;      // RTC_CASTS_SHADOW
+    int32_t root;        // BvhNode index of the root
+    int32_t n_tris;
+    float lo[3], hi[3];  // object-space root box (outward rounded)
+    float bound_abs[3];  // max |coordinate| of the root box per axis: scales the f32 slab error bound
+    float pad[3];
+};
+static_assert(sizeof(DMesh) % 16 == 0, "DMesh alignment");
+
+// CSG evaluation program (compiled from rtc_node trees): int4 words {op, a, b, c}.
+enum CsgOpcode {
+    CSG_OP_LEAF = 0,    // a = leaf: append its intersections as a new segment
+    CSG_OP_BBOX = 1,    // a = rtc_node index, b = pc to jump to (after pushing an empty segment) on a miss
+    CSG_OP_MERGE = 2,   // a = n: fuse the top n segments (group.zig:52-58)
+    CSG_OP_FILTER = 3,  // a = rtc_csg_op, b,c = leaf range of the LEFT operand: fuse top 2, sort, filter
+    CSG_OP_END = 4
+};
+struct DCsgRoot {
+    int32_t pc;                    // first program word
+    int32_t leaf_begin, leaf_end;  // leaves owned by this object
+    int32_t pad;
+};
+
+struct DScene {
+    const rtc_light* lights;
+    const rtc_material* materials;
+    const rtc_pattern* patterns;
+    const rtc_uv_pattern* uvs;
+    const rtc_image* images;
+    const uint8_t* texels;
+    const rtc_transform* transforms;
+    const rtc_leaf* leaves;
+    const rtc_tri_normals* normals;  // indexed by rtc_leaf.triangle
+    const rtc_triangle* blob_tris;   // original order (CSG operands, guarded triangles)
+    const rtc_guard* guards;
+    const rtc_node* nodes;
+    const int32_t* prims;  // top-level analytic leaves (and triangles kept out of meshes)
+    const DMesh* meshes;
+    const BvhNode* bvh;
+    const DTri* tris;
+    const int4* csg_prog;
+    const DCsgRoot* csg_roots;
+    int32_t n_lights, n_prims, n_meshes, n_csg;
+    int32_t n_leaves, bvh_max_depth;
+};
+
+}  // namespace rtc

@@ -1,0 +1,342 @@
+// The render kernel: Camera.render / renderWorker (camera.zig:80-125) + World.colorAt and everything
+// below it (world.zig:86-189, 212-289) for every pixel of a partition of the frame.
+//
+// Execution model:
+//   * persistent threads: the grid is sized to the machine (SMs x resident CTAs); warps pull pixels
+//     from a global atomic counter, 32-pixel 8x4 tiles at a time when a whole warp is idle, single
+//     pixels (ballot + popc ranked) when only some lanes are;
+//   * the recursion colorAt -> shadeHit -> reflectedColor/refractedColor -> colorAt is unrolled
+//     into a per-lane state machine.  shadeHit is linear in the colours its children return, so a
+//     ray carries the product of the factors on its path (reflective, transparency, Schlick) and
+//     adds weight x surface to the pixel; pending children sit on a per-lane stack of <= 6 rays;
+//   * every trip through the loop each live lane runs exactly ONE world query (closest hit, shadow
+//     any-hit or the containers scan), so lanes in different shading stages still share the
+//     traversal code and the warp stays converged where the time goes.
+#include <cuda_runtime.h>
+
+#include "render_params.h"
+#include "rt_pattern.cuh"
+#include "rt_trace.cuh"
+
+namespace rtc {
+
+struct RayTask {
+    double ox, oy, oz, dx, dy, dz, w;
+    int remaining, pad;
+};
+#define RTC_RAY_STACK 8
+
+enum { ST_IDLE = 0, ST_CLOSEST = 1, ST_CONTAINERS = 2, ST_SHADOW = 3 };
+
+// color.zig:61-71 : round half away from zero, clamped to [0,255]
+__device__ __forceinline__ unsigned char quantise(double c) {
+    double t = round(c * 255.0);
+    if (!(t > 0.0)) return 0;
+    if (t > 255.0) return 255;
+    return (unsigned char)t;
+}
+
+__global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParams P) {
+    __shared__ int s_stack[RTC_BVH_STACK * RTC_BLOCK];
+    int* stack = s_stack + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    int state = ST_IDLE;
+    bool done = false;
+    int err = 0;
+    unsigned long long n_primary = 0, n_shadow = 0, n_secondary = 0;
+
+    // current ray
+    V3 ro = v3(0, 0, 0), rd = v3(0, 0, 1);
+    double rw = 0.0;
+    int remaining = 0;
+    // current pixel
+    long long pix = -1;
+    V3 pcol = v3(0, 0, 0);
+    // current hit (valid in ST_CONTAINERS / ST_SHADOW)
+    Hit hit = {0, -1, 0, 0};
+    V3 h_point = v3(0, 0, 0), h_normal = v3(0, 0, 0), h_over = v3(0, 0, 0);
+    V3 h_color = v3(0, 0, 0), h_surface = v3(0, 0, 0);
+    double h_n1 = 1.0, h_n2 = 1.0;
+    int h_mat = 0, h_light = 0;
+
+    RayTask rays[RTC_RAY_STACK];
+    int rsp = 0;
+
+    Query q;
+    q.mode = Q_CLOSEST;
+    q.o = ro;
+    q.d = rd;
+    q.inv_d = rd;
+    q.t_max = 0;
+    q.best = hit;
+    q.shadowed = false;
+    q.cont = {0, -1, 0, -1, 0, 0};
+
+    for (;;) {
+        // ---- refill idle lanes ------------------------------------------------------------------
+        unsigned need = __ballot_sync(0xffffffffu, state == ST_IDLE && !done);
+        if (need) {
+            unsigned long long base = 0;
+            int leader = __ffs(need) - 1;
+            if ((int)lane == leader) base = atomicAdd(P.counters, (unsigned long long)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (state == ST_IDLE && !done) {
+                unsigned long long item = base + __popc(need & lt_mask);
+                if (item >= P.n_items) {
+                    done = true;
+                } else {
+                    // 8x4 pixel tiles, row-major tiles over the packed rows of this partition
+                    unsigned long long tile = item >> 5;
+                    unsigned in = (unsigned)(item & 31u);
+                    unsigned long long px = (tile % P.tiles_x) * 8ull + (in & 7u);
+                    unsigned long long pr = (tile / P.tiles_x) * 4ull + (in >> 3);
+                    if (px < P.cam.hsize && pr < P.rows) {
+                        unsigned long long y = ((pr / P.tile_rows) * P.n_parts + P.part) * P.tile_rows + pr % P.tile_rows;
+                        // Camera.rayForPixel (camera.zig:64-76)
+                        double xoffset = ((double)px + 0.5) * P.cam.pixel_size;
+                        double yoffset = ((double)y + 0.5) * P.cam.pixel_size;
+                        double wx = P.cam.half_width - xoffset;
+                        double wy = P.cam.half_height - yoffset;
+                        const double* m = P.cam.inv;
+                        V3 pixel = v3(m[0] * wx + m[1] * wy + m[2] * -1.0 + m[3], m[4] * wx + m[5] * wy + m[6] * -1.0 + m[7],
+                                      m[8] * wx + m[9] * wy + m[10] * -1.0 + m[11]);
+                        V3 origin = v3(m[3], m[7], m[11]);
+                        ro = origin;
+                        rd = normalized(pixel - origin);
+                        rw = 1.0;
+                        remaining = P.max_depth;
+                        pix = (long long)(pr * P.cam.hsize + px);
+                        pcol = v3(0, 0, 0);
+                        rsp = 0;
+                        state = ST_CLOSEST;
+                        n_primary++;
+                    }
+                    // items outside the frame are simply dropped: the lane asks again next trip
+                }
+            }
+        }
+        if (__all_sync(0xffffffffu, done && state == ST_IDLE)) break;
+
+        // ---- one world query per live lane --------------------------------------------------------
+        if (state != ST_IDLE) {
+            if (state == ST_CLOSEST) {
+                q.mode = Q_CLOSEST;
+                q.o = ro;
+                q.d = rd;
+                q.best.t = RTC_INF;
+                q.best.leaf = -1;
+                q.best.u = q.best.v = 0.0;
+            } else if (state == ST_SHADOW) {  // World.isShadowed (world.zig:126-135)
+                const rtc_light& Lg = S.lights[h_light];
+                V3 dir = v3(Lg.position[0], Lg.position[1], Lg.position[2]) - h_over;
+                double dist = sqrt(dot(dir, dir));
+                q.mode = Q_SHADOW;
+                q.o = h_over;
+                q.d = v3(dir.x / dist, dir.y / dist, dir.z / dist);
+                q.t_max = dist;
+                q.shadowed = false;
+                n_shadow++;
+            } else {
+                q.mode = Q_CONTAINERS;
+                q.o = ro;
+                q.d = rd;
+                q.cont.hit_t = hit.t;
+                q.cont.hit_leaf = hit.leaf;
+                q.cont.c_t = -RTC_INF;
+                q.cont.c_leaf = -1;
+                q.cont.hit_odd = 0;
+                q.cont.hit_last_t = -RTC_INF;
+            }
+            trace(q, S, stack, &err);
+        }
+
+        // ---- consume the result -----------------------------------------------------------------------
+        bool pop_next = false;
+        if (state == ST_CLOSEST) {
+            if (q.best.leaf < 0) {
+                pop_next = true;  // colorAt: no hit -> black (world.zig:119-121)
+            } else {
+                // PreComputations.new (world.zig:212-227)
+                hit = q.best;
+                const rtc_leaf& L = S.leaves[hit.leaf];
+                M34 inv = load_m34(S.transforms[L.transform].inverse);
+                h_point = ro + rd * hit.t;
+                int kind = L.kind;
+                V3 lp = xf_point(inv, h_point);  // Shape.normalAt (shape.zig:338-350)
+                double u = hit.u, v = hit.v;
+                const double* nrm = nullptr;
+                if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
+                    nrm = S.normals[L.triangle].n;
+                    if (kind == RTC_SMOOTH_TRIANGLE) {
+                        // u,v of a triangle found outside the mesh path: same ray, same test, same values
+                        const rtc_triangle& T = S.blob_tris[L.triangle];
+                        double tt;
+                        tri_intersect(v3(T.p1[0], T.p1[1], T.p1[2]), v3(T.e1[0], T.e1[1], T.e1[2]),
+                                      v3(T.e2[0], T.e2[1], T.e2[2]), xf_point(inv, ro), xf_vec(inv, rd), tt, u, v);
+                    }
+                }
+                V3 ln = leaf_local_normal(kind, L.minimum, L.maximum, lp, nrm, u, v);
+                V3 n = xf_normal(inv, ln);
+                if (dot(n, neg(rd)) < 0.0) n = neg(n);
+                h_normal = n;
+                h_over = h_point + n * 1e-5;
+                h_mat = L.material;
+                const rtc_material& M = S.materials[h_mat];
+                // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
+                // it is the same colour each time, so once per hit.
+                h_color = pattern_color(S, M.pattern, xf_point(inv, h_over), &err);
+                h_surface = v3(0, 0, 0);
+                h_light = 0;
+                h_n1 = 1.0;
+                h_n2 = 1.0;
+                // n1/n2 only reach a result through refractedColor / schlick, both gated on
+                // transparency (world.zig:101-102, :178)
+                if (M.transparency != 0.0) state = ST_CONTAINERS;
+                else state = S.n_lights > 0 ? ST_SHADOW : ST_IDLE;
+                if (state == ST_IDLE) state = -1;  // no lights: fall through to the children below
+            }
+        } else if (state == ST_CONTAINERS) {
+            const Containers& c = q.cont;
+            double ri_hit = S.materials[S.leaves[hit.leaf].material].refractive_index;
+            double ri_c = c.c_leaf >= 0 ? S.materials[S.leaves[c.c_leaf].material].refractive_index : 1.0;
+            if (c.hit_odd) {
+                bool hit_is_last = c.c_leaf < 0 || c.hit_last_t > c.c_t || (c.hit_last_t == c.c_t && hit.leaf > c.c_leaf);
+                h_n1 = hit_is_last ? ri_hit : ri_c;
+                h_n2 = ri_c;
+            } else {
+                h_n1 = ri_c;
+                h_n2 = ri_hit;
+            }
+            state = S.n_lights > 0 ? ST_SHADOW : -1;
+        } else if (state == ST_SHADOW) {
+            // Material.lighting (material.zig:40-74)
+            const rtc_light& Lg = S.lights[h_light];
+            const rtc_material& M = S.materials[h_mat];
+            V3 li = v3(Lg.intensity[0], Lg.intensity[1], Lg.intensity[2]);
+            V3 eff = v3(h_color.x * li.x, h_color.y * li.y, h_color.z * li.z);
+            V3 sum = eff * M.ambient;
+            if (!q.shadowed) {
+                V3 lightv = q.d;  // == normalize(light.position - over_point)
+                double ldn = dot(lightv, h_normal);
+                if (ldn >= 0.0) {
+                    V3 diffuse = eff * (M.diffuse * ldn);
+                    V3 reflectv = lightv - h_normal * (2.0 * dot(lightv, h_normal));  // tuple.zig reflect
+                    double rde = dot(neg(reflectv), neg(rd));
+                    V3 spec = v3(0, 0, 0);
+                    if (rde > 0.0) spec = li * (M.specular * pow(rde, M.shininess));
+                    sum = sum + diffuse + spec;
+                }
+            }
+            h_surface = h_surface + sum;
+            h_light++;
+            if (h_light >= S.n_lights) state = -1;
+        }
+
+        if (state == -1) {
+            // shadeHit tail (world.zig:97-107) with the children deferred onto the ray stack
+            const rtc_material& M = S.materials[h_mat];
+            pcol = pcol + h_surface * rw;
+            V3 eyev = neg(rd);
+            double refl_w = 0.0, refr_w = 0.0;
+            V3 refr_dir = v3(0, 0, 0);
+            bool spawn_refl = remaining > 0 && M.reflective != 0.0;  // reflectedColor (world.zig:157-167)
+            if (spawn_refl) refl_w = M.reflective;
+            // refractedColor (world.zig:171-189)
+            double n_ratio = h_n1 / h_n2;
+            double cos_i = dot(eyev, h_normal);
+            double sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
+            bool spawn_refr = !(sin2_t > 1.0) && remaining > 0 && M.transparency != 0.0;
+            if (spawn_refr) {
+                double cos_t = sqrt(1.0 - sin2_t);
+                refr_dir = h_normal * (n_ratio * cos_i - cos_t) - eyev * n_ratio;
+                refr_w = M.transparency;
+            }
+            if (M.reflective > 0.0 && M.transparency > 0.0) {  // schlick (world.zig:272-289)
+                double cosv = cos_i;
+                double reflectance;
+                bool tir = false;
+                if (h_n1 > h_n2) {
+                    double nr = h_n1 / h_n2;
+                    double s2 = nr * nr * (1.0 - cosv * cosv);
+                    if (s2 > 1.0) tir = true;
+                    else cosv = sqrt(1.0 - s2);
+                }
+                if (tir) {
+                    reflectance = 1.0;
+                } else {
+                    double frac = (h_n1 - h_n2) / (h_n1 + h_n2);
+                    double r0 = frac * frac;
+                    double x = 1.0 - cosv;
+                    reflectance = r0 + (1.0 - r0) * (x * x * x * x * x);
+                }
+                refl_w *= reflectance;
+                refr_w *= (1.0 - reflectance);
+            }
+            if (spawn_refr) {
+                V3 under = h_point - h_normal * 1e-5;
+                if (rsp < RTC_RAY_STACK) {
+                    rays[rsp++] = {under.x, under.y, under.z, refr_dir.x, refr_dir.y, refr_dir.z, rw * refr_w, remaining - 1, 0};
+                }
+                n_secondary++;
+            }
+            if (spawn_refl) {
+                V3 reflectv = rd - h_normal * (2.0 * dot(rd, h_normal));
+                if (rsp < RTC_RAY_STACK) {
+                    rays[rsp++] = {h_over.x, h_over.y, h_over.z, reflectv.x, reflectv.y, reflectv.z, rw * refl_w, remaining - 1, 0};
+                }
+                n_secondary++;
+            }
+            pop_next = true;
+        }
+
+        if (pop_next) {
+            if (rsp > 0) {
+                RayTask tk = rays[--rsp];
+                ro = v3(tk.ox, tk.oy, tk.oz);
+                rd = v3(tk.dx, tk.dy, tk.dz);
+                rw = tk.w;
+                remaining = tk.remaining;
+                state = ST_CLOSEST;
+            } else {
+                if (P.out8) {
+                    uchar4 c = make_uchar4(quantise(pcol.x), quantise(pcol.y), quantise(pcol.z), 255);
+                    reinterpret_cast<uchar4*>(P.out8)[pix] = c;
+                } else {
+                    double* o = P.out + pix * 3;
+                    o[0] = pcol.x;
+                    o[1] = pcol.y;
+                    o[2] = pcol.z;
+                }
+                state = ST_IDLE;
+            }
+        }
+    }
+
+    // ---- ray counters: warp reduce, one atomic per warp -------------------------------------------
+    for (int s = 16; s > 0; s >>= 1) {
+        n_primary += __shfl_down_sync(0xffffffffu, n_primary, s);
+        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, s);
+        n_secondary += __shfl_down_sync(0xffffffffu, n_secondary, s);
+        err |= __shfl_down_sync(0xffffffffu, err, s);
+    }
+    if (lane == 0) {
+        atomicAdd(P.counters + 1, n_primary);
+        atomicAdd(P.counters + 2, n_shadow);
+        atomicAdd(P.counters + 3, n_secondary);
+        if (err) atomicOr(P.counters + 4, (unsigned long long)err);
+    }
+}
+
+// Host-side launcher used by scene_device.cu
+int launch_render(const DScene& S, const RenderParams& P, int grid, cudaStream_t stream) {
+    render_kernel<<<grid, RTC_BLOCK, 0, stream>>>(S, P);
+    return (int)cudaGetLastError();
+}
+
+int render_kernel_occupancy(int* blocks_per_sm) {
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel, RTC_BLOCK, 0);
+}
+
+}  // namespace rtc

@@ -1,0 +1,317 @@
+// extern "C" surface declared in include/rtc_b200.h: scene upload, render calls, host loader.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "host/flatten.hpp"
+#include "host/loader.hpp"
+#include "render_params.h"
+#include "scene_build.hpp"
+
+using namespace rtc;
+
+static thread_local std::string g_error;
+static thread_local int g_device = 0;
+
+static int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+#define CUDA_TRY(expr)                                                                             \
+    do {                                                                                           \
+        cudaError_t e_ = (expr);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(RTC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+struct rtc_scene {
+    int device = 0;
+    void* slab = nullptr;  // one allocation holding every array of the scene
+    size_t slab_bytes = 0;
+    DScene d{};
+    unsigned long long* d_counters = nullptr;  // 8 x u64
+    double* d_frame = nullptr;                 // scratch framebuffer for the host-output entry points
+    size_t d_frame_bytes = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int grid = 0;
+};
+
+extern "C" {
+
+const char* rtc_last_error(void) { return g_error.c_str(); }
+
+int rtc_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int rtc_set_device(int device) {
+    if (device < 0 || device >= rtc_device_count()) return fail(RTC_ERR_CUDA, "rtc_set_device: no such CUDA device");
+    g_device = device;
+    return RTC_OK;
+}
+
+uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part) {
+    if (!part || part->n_parts <= 1) return vsize;
+    uint64_t tr = part->tile_rows ? part->tile_rows : 1, rows = 0;
+    uint64_t n_tiles = (vsize + tr - 1) / tr;
+    for (uint64_t t = part->part; t < n_tiles; t += part->n_parts) {
+        uint64_t y0 = t * tr, y1 = y0 + tr < vsize ? y0 + tr : vsize;
+        rows += y1 - y0;
+    }
+    return rows;
+}
+
+void rtc_scene_destroy(rtc_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->slab) cudaFree(s->slab);
+    if (s->d_counters) cudaFree(s->d_counters);
+    if (s->d_frame) cudaFree(s->d_frame);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    delete s;
+}
+
+int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
+    if (!out) return fail(RTC_ERR_INVALID, "rtc_scene_create: out is NULL");
+    *out = nullptr;
+    if (rtc_device_count() <= 0) return fail(RTC_ERR_CUDA, "rtc_scene_create: no CUDA device (there is no CPU fallback)");
+    HostScene hs;
+    try {
+        build_host_scene(blob, nbytes, hs);
+    } catch (const std::exception& e) {
+        return fail(RTC_ERR_INVALID, e.what());
+    }
+    if (hs.bvh_max_depth >= 64) return fail(RTC_ERR_CAPACITY, "BVH deeper than the traversal stack");
+    if (hs.csg_max_segments > 16) return fail(RTC_ERR_CAPACITY, "CSG nesting deeper than the segment stack");
+
+    rtc_scene* s = new rtc_scene();
+    s->device = g_device;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e != cudaSuccess) {
+        delete s;
+        return fail(RTC_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    }
+    // ---- one slab, 256-byte aligned sections, one H2D copy --------------------------------------
+    std::vector<uint8_t> stage;
+    auto put = [&](const void* p, size_t bytes) -> size_t {
+        size_t off = (stage.size() + 255) & ~size_t(255);
+        stage.resize(off + bytes);
+        if (bytes) std::memcpy(&stage[off], p, bytes);
+        return off;
+    };
+#define PUT(vec) put((vec).data(), (vec).size() * sizeof((vec)[0]))
+    size_t o_lights = PUT(hs.lights), o_mat = PUT(hs.materials), o_pat = PUT(hs.patterns), o_uv = PUT(hs.uvs);
+    size_t o_img = PUT(hs.images), o_tex = PUT(hs.texels), o_xf = PUT(hs.transforms), o_leaf = PUT(hs.leaves);
+    size_t o_nrm = PUT(hs.normals), o_btri = PUT(hs.blob_tris), o_guard = PUT(hs.guards), o_node = PUT(hs.nodes);
+    size_t o_prim = PUT(hs.prims), o_mesh = PUT(hs.meshes), o_bvh = PUT(hs.bvh), o_tri = PUT(hs.tris);
+    size_t o_prog = PUT(hs.csg_prog), o_root = PUT(hs.csg_roots);
+#undef PUT
+    s->slab_bytes = stage.size() + 256;
+    auto bail = [&](cudaError_t err, const char* what) {
+        std::string msg = std::string(what) + ": " + cudaGetErrorString(err);
+        rtc_scene_destroy(s);
+        return fail(RTC_ERR_CUDA, msg);
+    };
+    if ((e = cudaMalloc(&s->slab, s->slab_bytes)) != cudaSuccess) return bail(e, "cudaMalloc(scene)");
+    if ((e = cudaMemcpy(s->slab, stage.data(), stage.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
+        return bail(e, "cudaMemcpy(scene)");
+    if ((e = cudaMalloc(&s->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(counters)");
+    if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    const uint8_t* b = static_cast<const uint8_t*>(s->slab);
+    DScene& d = s->d;
+    d.lights = (const rtc_light*)(b + o_lights);
+    d.materials = (const rtc_material*)(b + o_mat);
+    d.patterns = (const rtc_pattern*)(b + o_pat);
+    d.uvs = (const rtc_uv_pattern*)(b + o_uv);
+    d.images = (const rtc_image*)(b + o_img);
+    d.texels = b + o_tex;
+    d.transforms = (const rtc_transform*)(b + o_xf);
+    d.leaves = (const rtc_leaf*)(b + o_leaf);
+    d.normals = (const rtc_tri_normals*)(b + o_nrm);
+    d.blob_tris = (const rtc_triangle*)(b + o_btri);
+    d.guards = (const rtc_guard*)(b + o_guard);
+    d.nodes = (const rtc_node*)(b + o_node);
+    d.prims = (const int32_t*)(b + o_prim);
+    d.meshes = (const DMesh*)(b + o_mesh);
+    d.bvh = (const BvhNode*)(b + o_bvh);
+    d.tris = (const DTri*)(b + o_tri);
+    d.csg_prog = (const int4*)(b + o_prog);
+    d.csg_roots = (const DCsgRoot*)(b + o_root);
+    d.n_lights = (int32_t)hs.lights.size();
+    d.n_prims = (int32_t)hs.prims.size();
+    d.n_meshes = (int32_t)hs.meshes.size();
+    d.n_csg = (int32_t)hs.csg_roots.size();
+    d.n_leaves = (int32_t)hs.leaves.size();
+    d.bvh_max_depth = hs.bvh_max_depth;
+
+    // persistent grid: every SM filled to the kernel's occupancy
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, s->device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+    int per_sm = 0;
+    if ((e = (cudaError_t)render_kernel_occupancy(&per_sm)) != cudaSuccess) return bail(e, "occupancy query");
+    if (per_sm < 1) per_sm = 1;
+    s->grid = prop.multiProcessorCount * per_sm;
+    *out = s;
+    return RTC_OK;
+}
+
+static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
+                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats) {
+    if (!s || !cam) return fail(RTC_ERR_INVALID, "render: NULL scene or camera");
+    if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
+    if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
+    rtc_partition whole = {1, 0, 1};
+    if (!part) part = &whole;
+    if (part->n_parts == 0 || part->part >= part->n_parts || part->tile_rows == 0)
+        return fail(RTC_ERR_INVALID, "render: bad partition");
+    CUDA_TRY(cudaSetDevice(s->device));
+    RenderParams P{};
+    P.cam.hsize = cam->hsize;
+    P.cam.vsize = cam->vsize;
+    P.cam.half_width = cam->half_width;
+    P.cam.half_height = cam->half_height;
+    P.cam.pixel_size = cam->pixel_size;
+    std::memcpy(P.cam.inv, cam->inverse, sizeof P.cam.inv);
+    P.max_depth = max_depth;
+    P.tile_rows = part->tile_rows;
+    P.part = part->part;
+    P.n_parts = part->n_parts;
+    P.rows = rtc_partition_rows(cam->vsize, part);
+    P.tiles_x = (unsigned)((cam->hsize + 7) / 8);
+    P.n_items = (unsigned long long)P.tiles_x * ((P.rows + 3) / 4) * 32ull;
+    P.out = d_rgb;
+    P.out8 = d_rgba;
+    P.counters = s->d_counters;
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    if (P.rows == 0) return RTC_OK;
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
+    CUDA_TRY(cudaEventRecord(s->ev0, stream));
+    CUDA_TRY((cudaError_t)launch_render(s->d, P, s->grid, stream));
+    CUDA_TRY(cudaEventRecord(s->ev1, stream));
+    unsigned long long c[8];
+    CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    if (stats) {
+        stats->primary_rays = c[1];
+        stats->shadow_rays = c[2];
+        stats->secondary_rays = c[3];
+        stats->pixels = P.rows * cam->hsize;
+        stats->kernel_ms = ms;
+        stats->launches = 1;
+    }
+    if (c[4]) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf,
+                      "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
+                      "4=CSG list, 8=BVH stack)",
+                      c[4]);
+        return fail(RTC_ERR_CAPACITY, buf);
+    }
+    return RTC_OK;
+}
+
+int rtc_render_device(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
+                      void* stream, rtc_stats* stats) {
+    if (!d_rgb) return fail(RTC_ERR_INVALID, "rtc_render_device: d_rgb is NULL");
+    return render_common(s, cam, max_depth, part, d_rgb, nullptr, (cudaStream_t)stream, stats);
+}
+
+static int ensure_frame(rtc_scene* s, size_t bytes) {
+    if (s->d_frame_bytes >= bytes) return RTC_OK;
+    if (s->d_frame) cudaFree(s->d_frame);
+    s->d_frame = nullptr;
+    s->d_frame_bytes = 0;
+    CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
+    s->d_frame_bytes = bytes;
+    return RTC_OK;
+}
+
+// copies the packed partition rows into their places in the caller's full frame
+static int scatter_rows(const rtc_camera* cam, const rtc_partition* part, const void* d_src, void* h_dst, size_t px_bytes) {
+    size_t row_bytes = (size_t)cam->hsize * px_bytes;
+    if (!part || part->n_parts <= 1) {
+        CUDA_TRY(cudaMemcpy(h_dst, d_src, row_bytes * cam->vsize, cudaMemcpyDeviceToHost));
+        return RTC_OK;
+    }
+    uint64_t tr = part->tile_rows, n_tiles = (cam->vsize + tr - 1) / tr, packed = 0;
+    for (uint64_t t = part->part; t < n_tiles; t += part->n_parts) {
+        uint64_t y0 = t * tr, y1 = y0 + tr < cam->vsize ? y0 + tr : cam->vsize;
+        CUDA_TRY(cudaMemcpy((char*)h_dst + y0 * row_bytes, (const char*)d_src + packed * row_bytes, (y1 - y0) * row_bytes,
+                            cudaMemcpyDeviceToHost));
+        packed += y1 - y0;
+    }
+    return RTC_OK;
+}
+
+int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* rgb_out,
+               rtc_stats* stats) {
+    if (!s || !cam || !rgb_out) return fail(RTC_ERR_INVALID, "rtc_render: NULL argument");
+    CUDA_TRY(cudaSetDevice(s->device));
+    uint64_t rows = rtc_partition_rows(cam->vsize, part);
+    int rc = ensure_frame(s, (size_t)rows * cam->hsize * 3 * sizeof(double) + 16);
+    if (rc) return rc;
+    rc = render_common(s, cam, max_depth, part, s->d_frame, nullptr, 0, stats);
+    if (rc) return rc;
+    return scatter_rows(cam, part, s->d_frame, rgb_out, 3 * sizeof(double));
+}
+
+int rtc_render_rgba8(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, uint8_t* rgba_out,
+                     rtc_stats* stats) {
+    if (!s || !cam || !rgba_out) return fail(RTC_ERR_INVALID, "rtc_render_rgba8: NULL argument");
+    CUDA_TRY(cudaSetDevice(s->device));
+    uint64_t rows = rtc_partition_rows(cam->vsize, part);
+    int rc = ensure_frame(s, (size_t)rows * cam->hsize * 4 + 16);
+    if (rc) return rc;
+    rc = render_common(s, cam, max_depth, part, nullptr, (unsigned char*)s->d_frame, 0, stats);
+    if (rc) return rc;
+    return scatter_rows(cam, part, s->d_frame, rgba_out, 4);
+}
+
+// ---- host loader -------------------------------------------------------------------------------------
+int rtc_load_scene_json(const char* json_text, const char* asset_dir, long width, long height, void** blob_out,
+                        size_t* nbytes_out, rtc_camera* cam_out) {
+    if (!json_text || !blob_out || !nbytes_out || !cam_out) return fail(RTC_ERR_INVALID, "rtc_load_scene_json: NULL argument");
+    try {
+        SceneInfo si = parse_scene(json_text, directory_loader(asset_dir ? asset_dir : ""), width, height);
+        std::vector<uint8_t> blob = flatten_world(si.world);
+        void* p = std::malloc(blob.size());
+        if (!p) return fail(RTC_ERR_INVALID, "out of memory");
+        std::memcpy(p, blob.data(), blob.size());
+        *blob_out = p;
+        *nbytes_out = blob.size();
+        *cam_out = flatten_camera(si.camera);
+        return RTC_OK;
+    } catch (const std::exception& e) {
+        return fail(RTC_ERR_PARSE, e.what());
+    }
+}
+
+void rtc_blob_free(void* blob) { std::free(blob); }
+
+int rtc_camera_look_at(rtc_camera* cam, const double from[3], const double to[3], const double up[3]) {
+    if (!cam || !from || !to || !up) return fail(RTC_ERR_INVALID, "rtc_camera_look_at: NULL argument");
+    try {
+        Mat4 view = Mat4::view_transform(Tuple::point(from[0], from[1], from[2]), Tuple::point(to[0], to[1], to[2]),
+                                         Tuple::vec3(up[0], up[1], up[2]));
+        Mat4 inv = view.inverse();
+        for (int r = 0; r < 4; r++)
+            for (int c = 0; c < 4; c++) cam->inverse[r * 4 + c] = inv.d[r][c];
+        return RTC_OK;
+    } catch (const std::exception& e) {
+        return fail(RTC_ERR_INVALID, e.what());
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,236 @@
+// Blob -> host-side arrays of the device scene: validation, mesh grouping + BVH build, CSG program
+// compilation.  Pure host code (no CUDA calls) so it can be unit-tested without a GPU.
+#include "scene_build.hpp"
+
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+
+#include "bvh.hpp"
+
+namespace rtc {
+namespace {
+
+template <class T>
+const T* section(const uint8_t* base, size_t nbytes, uint64_t off, uint64_t count, const char* what) {
+    if (off % 16 != 0 || off > nbytes || count > (nbytes - off) / sizeof(T))
+        throw std::runtime_error(std::string("blob: section out of range: ") + what);
+    return reinterpret_cast<const T*>(base + off);
+}
+
+void check_index(int64_t v, int64_t n, const char* what, bool allow_neg = false) {
+    if (allow_neg && v == -1) return;
+    if (v < 0 || v >= n) throw std::runtime_error(std::string("blob: index out of range: ") + what);
+}
+
+struct CsgCompiler {
+    const std::vector<rtc_node>& nodes;
+    const std::vector<int32_t>& children;
+    std::vector<int4>& prog;
+    int depth = 0, max_depth = 0;
+
+    void push_seg() {
+        depth++;
+        if (depth > max_depth) max_depth = depth;
+    }
+    void compile(int32_t ni) {
+        const rtc_node& n = nodes[(size_t)ni];
+        size_t bbox_at = (size_t)-1;
+        if (n.kind != RTC_NODE_LEAF && n.use_bbox) {
+            bbox_at = prog.size();
+            prog.push_back(make_int4(CSG_OP_BBOX, ni, 0, 0));
+        }
+        int d0 = depth;
+        if (n.kind == RTC_NODE_LEAF) {
+            prog.push_back(make_int4(CSG_OP_LEAF, n.a, 0, 0));
+            push_seg();
+        } else if (n.kind == RTC_NODE_GROUP) {
+            if (n.b == 0) {
+                prog.push_back(make_int4(CSG_OP_MERGE, 0, 0, 0));
+                push_seg();
+            }
+            for (int32_t k = 0; k < n.b; k++) {
+                compile(children[(size_t)(n.a + k)]);
+                if (k > 0) {
+                    prog.push_back(make_int4(CSG_OP_MERGE, 2, 0, 0));
+                    depth--;
+                }
+            }
+        } else {
+            compile(n.a);
+            compile(n.b);
+            const rtc_node& l = nodes[(size_t)n.a];
+            prog.push_back(make_int4(CSG_OP_FILTER, n.op, l.leaf_begin, l.leaf_end));
+            depth--;
+        }
+        if (depth != d0 + 1) throw std::runtime_error("csg compile: segment accounting");
+        if (bbox_at != (size_t)-1) prog[bbox_at].z = (int)prog.size();
+    }
+};
+
+}  // namespace
+
+void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
+    if (!blob || nbytes < sizeof(rtc_blob_header)) throw std::runtime_error("blob: too small");
+    const uint8_t* base = static_cast<const uint8_t*>(blob);
+    rtc_blob_header h;
+    std::memcpy(&h, base, sizeof h);
+    if (h.magic != RTC_BLOB_MAGIC) throw std::runtime_error("blob: bad magic");
+    if (h.version != RTC_BLOB_VERSION) throw std::runtime_error("blob: unsupported version");
+    if (h.total_bytes != nbytes) throw std::runtime_error("blob: size mismatch");
+
+    auto copy = [&](auto& vec, uint64_t off, uint64_t n, const char* what) {
+        using T = typename std::remove_reference<decltype(vec)>::type::value_type;
+        const T* p = section<T>(base, nbytes, off, n, what);
+        vec.assign(p, p + n);
+    };
+    copy(hs.lights, h.off_lights, h.n_lights, "lights");
+    copy(hs.materials, h.off_materials, h.n_materials, "materials");
+    copy(hs.patterns, h.off_patterns, h.n_patterns, "patterns");
+    copy(hs.uvs, h.off_uv_patterns, h.n_uv_patterns, "uv patterns");
+    copy(hs.images, h.off_images, h.n_images, "images");
+    copy(hs.transforms, h.off_transforms, h.n_transforms, "transforms");
+    copy(hs.leaves, h.off_leaves, h.n_leaves, "leaves");
+    copy(hs.blob_tris, h.off_triangles, h.n_triangles, "triangles");
+    copy(hs.normals, h.off_tri_normals, h.n_triangles, "triangle normals");
+    copy(hs.guards, h.off_guards, h.n_guards, "guards");
+    copy(hs.nodes, h.off_nodes, h.n_nodes, "nodes");
+    std::vector<int32_t> children, roots;
+    copy(children, h.off_children, h.n_children, "children");
+    copy(roots, h.off_csg_roots, h.n_csg_roots, "csg roots");
+    copy(hs.texels, h.off_texels, h.texel_bytes, "texels");
+
+    // ---- validate every index the kernels will follow --------------------------------------------
+    for (auto& m : hs.materials) check_index(m.pattern, h.n_patterns, "material.pattern");
+    for (auto& p : hs.patterns) {
+        check_index(p.a, h.n_patterns, "pattern.a", true);
+        check_index(p.b, h.n_patterns, "pattern.b", true);
+        bool binary = p.kind == RTC_PAT_BLEND || p.kind == RTC_PAT_STRIPES || p.kind == RTC_PAT_GRADIENT ||
+                      p.kind == RTC_PAT_RADIAL_GRADIENT || p.kind == RTC_PAT_RINGS || p.kind == RTC_PAT_CHECKERS;
+        if (binary && (p.a < 0 || p.b < 0)) throw std::runtime_error("blob: pattern needs two children");
+        if (p.kind == RTC_PAT_PERTURB && p.a < 0) throw std::runtime_error("blob: perturb needs a child");
+        if (p.kind == RTC_PAT_TEXTURE_MAP) {
+            int n = p.mapping == RTC_MAP_CUBIC ? 6 : 1;
+            for (int i = 0; i < n; i++) check_index(p.uv[i], h.n_uv_patterns, "pattern.uv");
+        }
+        if (p.kind < 0 || p.kind > RTC_PAT_TEST) throw std::runtime_error("blob: pattern kind");
+    }
+    for (auto& u : hs.uvs) {
+        if (u.kind == RTC_UV_IMAGE) check_index(u.image, h.n_images, "uv.image");
+        int n = u.kind == RTC_UV_ALIGN_CHECK ? 5 : u.kind == RTC_UV_CHECKERS ? 2 : 0;
+        for (int i = 0; i < n; i++) check_index(u.sub[i], h.n_patterns, "uv.sub");
+    }
+    for (auto& im : hs.images) {
+        if (im.width <= 0 || im.height <= 0) throw std::runtime_error("blob: image size");
+        uint64_t bytes = (uint64_t)im.width * im.height * (im.format == RTC_IMG_RGBA8 ? 4 : 24);
+        if (im.offset % 16 || im.offset > h.texel_bytes || bytes > h.texel_bytes - im.offset)
+            throw std::runtime_error("blob: image texels out of range");
+    }
+    for (auto& l : hs.leaves) {
+        check_index(l.transform, h.n_transforms, "leaf.transform");
+        check_index(l.material, h.n_materials, "leaf.material");
+        check_index(l.guard, h.n_guards, "leaf.guard", true);
+        bool tri = l.kind == RTC_TRIANGLE || l.kind == RTC_SMOOTH_TRIANGLE;
+        if (tri) check_index(l.triangle, h.n_triangles, "leaf.triangle");
+        if (l.kind < 0 || l.kind > RTC_TEST_SHAPE) throw std::runtime_error("blob: leaf kind");
+    }
+    for (auto& g : hs.guards) check_index(g.next, h.n_guards, "guard.next", true);
+    for (size_t i = 0; i < hs.nodes.size(); i++) {
+        const rtc_node& n = hs.nodes[i];
+        if (n.kind == RTC_NODE_LEAF) check_index(n.a, h.n_leaves, "node.leaf");
+        else if (n.kind == RTC_NODE_CSG) {
+            // children precede parents (post-order emission) => no cycles
+            if (n.a < 0 || n.b < 0 || (size_t)n.a >= i || (size_t)n.b >= i) throw std::runtime_error("blob: csg operands");
+        } else if (n.kind == RTC_NODE_GROUP) {
+            if (n.a < 0 || n.b < 0 || (uint64_t)n.a + (uint64_t)n.b > h.n_children) throw std::runtime_error("blob: group children");
+            for (int32_t k = 0; k < n.b; k++)
+                if (children[(size_t)(n.a + k)] < 0 || (size_t)children[(size_t)(n.a + k)] >= i)
+                    throw std::runtime_error("blob: group child order");
+        } else {
+            throw std::runtime_error("blob: node kind");
+        }
+        if (n.leaf_begin < 0 || n.leaf_end < n.leaf_begin || (uint32_t)n.leaf_end > h.n_leaves)
+            throw std::runtime_error("blob: node leaf range");
+    }
+
+    // ---- which leaves belong to CSG objects --------------------------------------------------------
+    std::vector<char> in_csg(hs.leaves.size(), 0);
+    for (int32_t r : roots) {
+        check_index(r, h.n_nodes, "csg root");
+        const rtc_node& n = hs.nodes[(size_t)r];
+        for (int32_t i = n.leaf_begin; i < n.leaf_end; i++) in_csg[(size_t)i] = 1;
+    }
+
+    // ---- widen the pre-test boxes a little (they are an optimisation, never a decision) ------------
+    for (auto& l : hs.leaves) {
+        if (l.flags & RTC_UNBOUNDED) continue;
+        for (int a = 0; a < 3; a++) {
+            double pad = 1e-9 * (std::fabs(l.wmin[a]) + std::fabs(l.wmax[a])) + 1e-12;
+            l.wmin[a] -= pad;
+            l.wmax[a] += pad;
+        }
+    }
+
+    // ---- top level: analytic prims, meshes ----------------------------------------------------------
+    std::map<std::pair<int32_t, uint32_t>, std::vector<DTri>> groups;
+    for (size_t i = 0; i < hs.leaves.size(); i++) {
+        if (in_csg[i]) continue;
+        const rtc_leaf& l = hs.leaves[i];
+        if (l.kind == RTC_TEST_SHAPE) continue;
+        bool tri = l.kind == RTC_TRIANGLE || l.kind == RTC_SMOOTH_TRIANGLE;
+        if (tri && l.guard < 0) {
+            const rtc_triangle& t = hs.blob_tris[(size_t)l.triangle];
+            DTri d;
+            std::memcpy(d.p1, t.p1, sizeof d.p1);
+            std::memcpy(d.e1, t.e1, sizeof d.e1);
+            std::memcpy(d.e2, t.e2, sizeof d.e2);
+            d.leaf = (int32_t)i;
+            d.pad = 0;
+            groups[{l.transform, l.flags & RTC_CASTS_SHADOW}].push_back(d);
+        } else {
+            hs.prims.push_back((int32_t)i);
+        }
+    }
+    hs.bvh_max_depth = 0;
+    for (auto& kv : groups) {
+        BvhBuild b = build_bvh(kv.second);
+        DMesh m{};
+        m.transform = kv.first.first;
+        m.flags = kv.first.second;
+        m.root = (int32_t)hs.bvh.size();
+        m.n_tris = (int32_t)b.tris.size();
+        for (int a = 0; a < 3; a++) {
+            m.lo[a] = b.lo[a];
+            m.hi[a] = b.hi[a];
+            m.bound_abs[a] = std::fmax(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
+        }
+        int32_t node_base = (int32_t)hs.bvh.size(), tri_base = (int32_t)hs.tris.size();
+        for (BvhNode n : b.nodes) {
+            if (n.n0 > 0) n.c0 += tri_base;
+            else if (n.c0 >= 0) n.c0 += node_base;
+            if (n.n1 > 0) n.c1 += tri_base;
+            else if (n.c1 >= 0) n.c1 += node_base;
+            hs.bvh.push_back(n);
+        }
+        hs.tris.insert(hs.tris.end(), b.tris.begin(), b.tris.end());
+        hs.meshes.push_back(m);
+        if (b.max_depth > hs.bvh_max_depth) hs.bvh_max_depth = b.max_depth;
+    }
+
+    // ---- CSG programs ------------------------------------------------------------------------------
+    CsgCompiler cc{hs.nodes, children, hs.csg_prog};
+    for (int32_t r : roots) {
+        DCsgRoot root{};
+        root.pc = (int32_t)hs.csg_prog.size();
+        root.leaf_begin = hs.nodes[(size_t)r].leaf_begin;
+        root.leaf_end = hs.nodes[(size_t)r].leaf_end;
+        cc.depth = 0;
+        cc.compile(r);
+        hs.csg_prog.push_back(make_int4(CSG_OP_END, 0, 0, 0));
+        hs.csg_roots.push_back(root);
+    }
+    hs.csg_max_segments = cc.max_depth;
+}
+
+}  // namespace rtc
