@@ -2,7 +2,10 @@
 PKG := ray-tracer-challenge_b200
 CSRC := $(PKG)/csrc
 NVCC ?= nvcc
-NVFLAGS ?= -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-Wall
+# -fmad=false: the reference (Zig, no fast-math) never fuses a*b+c; keeping IEEE mul+add makes t values,
+# tie-breaks and pattern cell decisions bit-identical to it (DESIGN.md "exact arithmetic").
+FMAD ?= false
+NVFLAGS ?= -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=$(FMAD) -Xcompiler -fPIC,-Wall
 SRC := $(CSRC)/render.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
        $(CSRC)/host/scene.cpp $(CSRC)/host/scene_parser.cpp $(CSRC)/host/obj.cpp $(CSRC)/host/images.cpp \
        $(CSRC)/host/flatten.cpp
@@ -10,7 +13,7 @@ HDR := $(wildcard $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh $(CSRC)/host/*.hpp inc
 
 all: $(PKG)/librtc_b200.so oracle
 
-$(PKG)/librtc_b200.so: $(SRC) $(HDR)
+$(PKG)/librtc_b200.so: $(SRC) $(HDR) Makefile
 	$(NVCC) $(NVFLAGS) -shared -o $@ $(SRC) -lz
 
 oracle:

@@ -1,5 +1,6 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.hpp).  ctypes-friendly entry points used by
 // tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+#include <cstdio>
 #include <cstring>
 #include <string>
 
@@ -72,3 +73,39 @@ void oracle_set_camera(void* h, const double from[3], const double to[3], const 
 void oracle_scene_free(void* h) { delete (rtc::SceneInfo*)h; }
 
 }  // extern "C"
+
+// Debug aid for tests: prints the recursion tree of one pixel (hit kind, t, n1, n2) to stdout.
+namespace {
+void debug_color_at(const rtc::World& w, const Ray& ray, size_t remaining, int indent) {
+    Intersections xs;
+    world_intersect(w, ray, xs);
+    long h = hit_index(xs);
+    if (h < 0) {
+        std::printf("%*smiss (remaining %zu, %zu intersections)\n", indent, "", remaining, xs.size());
+        return;
+    }
+    Comps c = prepare_computations(xs[(size_t)h], ray, xs);
+    const rtc::Shape& o = *c.intersection.object;
+    std::printf("%*shit kind=%d id=%zu t=%.17g n1=%.6g n2=%.6g refl=%.3g transp=%.3g remaining=%zu nxs=%zu hit_index=%ld\n", indent, "",
+                (int)o.kind, o.id, c.intersection.t, c.n1, c.n2, o.material.reflective, o.material.transparency, remaining,
+                xs.size(), h);
+    if (remaining > 0 && o.material.reflective != 0.0) {
+        std::printf("%*sreflect:\n", indent, "");
+        debug_color_at(w, Ray{c.over_point, c.reflectv}, remaining - 1, indent + 2);
+    }
+    double n_ratio = c.n1 / c.n2, cos_i = c.eyev.dot(c.normal), sin2_t = n_ratio * n_ratio * (1.0 - cos_i * cos_i);
+    if (!(sin2_t > 1.0) && remaining > 0 && o.material.transparency != 0.0) {
+        double cos_t = std::sqrt(1.0 - sin2_t);
+        rtc::Tuple dir = c.normal.mul(n_ratio * cos_i - cos_t).sub(c.eyev.mul(n_ratio));
+        std::printf("%*srefract:\n", indent, "");
+        debug_color_at(w, Ray{c.under_point, dir}, remaining - 1, indent + 2);
+    } else if (o.material.transparency != 0.0) {
+        std::printf("%*sno refraction (sin2_t=%.6g)\n", indent, "", sin2_t);
+    }
+}
+}  // namespace
+
+extern "C" void oracle_debug_pixel(void* h, long x, long y, int max_depth) {
+    auto* s = (rtc::SceneInfo*)h;
+    debug_color_at(s->world, ray_for_pixel(s->camera, (size_t)x, (size_t)y), (size_t)max_depth, 0);
+}
