@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s and frame time of the hot path on BASELINE.json's headline config.
+
+Workload (config.workload): scenes/dragons.json rendered at 1920x1080, recursion depth 5, f64 —
+the configuration BASELINE.json quotes its target on.  One "step" = one frame.
+
+  value   Mrays/s (primary + shadow + secondary rays, counted on the device) with the scene resident
+          in HBM and the frame left in HBM (rtc_render_device), CUDA-event timed, L2 flushed between
+          steps (the scene, ~30 MB, would otherwise sit in the 126 MB L2).
+  e2e     the same metric through the reference-facing call Camera.render(world) -> host Canvas
+          (rtc_render): camera in, kernel, device->host copy of the f64 frame, all inside the timed
+          region.  The world stays uploaded between frames, the reference's own "preheated"
+          convention (README.md:122-125, lib.zig:166-190).
+  N > 1   one process per GPU (torchrun); rank r renders the interleaved 8-row tiles r, r+N, ... and
+          the packed rows are gathered to rank 0 over NCCL.  Strong scaling (same frame).
+  --impl reference   the CPU restatement of the reference algorithm (oracle/, all host threads) on a
+          bounded sample of the same frame (the reference itself is Zig: unavailable on this box).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+SCENE, WIDTH, HEIGHT, DEPTH, TILE_ROWS = "dragons", 1920, 1080, 5, 8
+# algorithmic bytes per ray for dragons.json = 13 two-child f32 nodes x 64 B +
+# 4 triangles x 72 B + 6 instance root tests x 64 B
+BYTES_PER_RAY = 1504
+
+
+def scene_source():
+    from tests import scenes
+    s = scenes.shipped_scene(SCENE)
+    if s is None:
+        raise SystemExit("bench: assets/_ref/scenes/%s.json is not staged; run __graft_entry__.build() where "
+                         "/root/reference is mounted" % SCENE)
+    return s
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons, sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+
+    def run(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.samples.append(float(f[0]))
+                self.max_mhz = float(f[1])
+                for n, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_sample(threads, bands=8, frac=0.125):
+    """Oracle on `bands` evenly spaced row bands covering `frac` of the frame -> (rays, seconds, desc)."""
+    from oracle import oracle_py
+    text, assets = scene_source()
+    sc = oracle_py.OracleScene(json_text=text, asset_dir=assets, width=WIDTH, height=HEIGHT)
+    rows = max(1, int(HEIGHT * frac / bands))
+    rays, secs = 0, 0.0
+    import numpy as np
+    out = np.zeros((HEIGHT, WIDTH, 3))
+    for b in range(bands):
+        y0 = int((b + 0.5) * HEIGHT / bands) - rows // 2
+        t = time.perf_counter()
+        _, c = sc.render(threads=threads, y0=y0, y1=y0 + rows)
+        secs += time.perf_counter() - t
+        rays += c["primary"] + c["shadow"] + c["secondary"]
+    return rays, secs, "%d bands x %d rows of the %dx%d frame (%.1f%% of the pixels)" % (
+        bands, rows, WIDTH, HEIGHT, 100.0 * bands * rows / HEIGHT)
+
+
+def base_line(args, n):
+    return {"metric": "Mrays/s", "unit": "Mrays/s", "n_gpus": n, "steps": args.steps, "warmup": args.warmup,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "scenes/dragons.json 1920x1080 depth 5 (6 x dragon.obj, 140,940 smooth triangles, "
+                                   "4 lights); the scene file IS the input, there is no random data",
+                       "l2": "flushed between steps (256 MiB memset)", "partition": "interleaved %d-row tiles" % TILE_ROWS}}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_sample(threads, bands=2, frac=0.004)
+    rays = secs = 0
+    desc = ""
+    for _ in range(args.steps):
+        r, s, desc = cpu_sample(threads)
+        rays, secs = rays + r, secs + s
+    v = rays / secs / 1e6
+    line = base_line(args, args.gpus)
+    line.update({"impl": "reference", "value": v, "ms_per_step": 1e3 * secs / args.steps,
+                 "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": desc},
+                 "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "note": "C++ restatement of the reference CPU algorithm (oracle/); the Zig reference cannot be built "
+                         "on this box; ms_per_step is the time of the SAMPLE, not of a full frame"})
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("ray-tracer-challenge_b200")
+    if not torch.cuda.is_available() or pkg.device_count() == 0:
+        raise SystemExit("bench: no CUDA device; this renderer has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    text, assets = scene_source()
+    t0 = time.perf_counter()
+    blob, cam = pkg.load_blob(text, assets, WIDTH, HEIGHT)
+    t1 = time.perf_counter()
+    wld = pkg.World(blob, local_rank)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    camera = pkg.Camera(cam)
+    part = (TILE_ROWS, rank, world)
+    rows = camera.partition_rows(part)
+    max_rows = max(camera.partition_rows((TILE_ROWS, r, world)) for r in range(world))
+    d_rows = torch.zeros((max_rows, WIDTH, 3), dtype=torch.float64, device=dev)   # this rank's packed rows
+    gathered = [torch.zeros_like(d_rows) for _ in range(world)] if (world > 1 and rank == 0) else None
+    frame = torch.zeros((HEIGHT, WIDTH, 3), dtype=torch.float64, device=dev) if rank == 0 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    # row index of every packed row of every rank, for the de-interleave on rank 0
+    row_maps = []
+    for r in range(world):
+        ys = [y for y in range(HEIGHT) if (y // TILE_ROWS) % world == r]
+        row_maps.append(torch.tensor(ys, dtype=torch.long, device=dev))
+
+    def step_device():
+        st = camera.render_device(wld, d_rows.data_ptr(), DEPTH, part, stream)
+        if world > 1:
+            dist.gather(d_rows, gathered, dst=0)
+            if rank == 0:
+                for r in range(world):
+                    frame.index_copy_(0, row_maps[r], gathered[r][: len(row_maps[r])])
+        return st
+
+    host = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
+
+    pinned = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64).pin_memory() if (world > 1 and rank == 0) else None
+
+    def step_e2e():
+        if world == 1:  # the public call: Camera.render(world) -> host Canvas
+            return camera.render(wld, DEPTH, None, out=host).stats
+        st = step_device()  # N > 1: render + NCCL gather, then the assembled frame goes to the host on rank 0
+        if rank == 0:
+            pinned.copy_(frame, non_blocking=False)
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    rays = kernel_ms = 0
+    launches = 0
+    wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()
+        barrier()
+        ev[i][0].record()
+        st = step_device()
+        ev[i][1].record()
+        rays += st.rays
+        kernel_ms += st.kernel_ms
+        launches += st.launches
+    barrier()
+    wall = time.perf_counter() - wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    # e2e leg (host buffers, D2H inside the timed region), wall clock bracketed by synchronize
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    e0 = time.perf_counter()
+    e_rays = 0
+    for i in range(args.steps):
+        e_rays += step_e2e().rays
+    barrier()
+    e_secs = time.perf_counter() - e0
+    sampler.stop_flag = True
+    sampler.join()
+
+    t = torch.tensor([dev_ms, e_secs], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays), float(e_rays), float(launches)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    dev_ms, e_secs = float(t[0]), float(t[1])
+    rays_all, e_rays_all, launches_all = float(tot[0]), float(tot[1]), int(tot[2])
+
+    if rank == 0:
+        peak, which = peaks()
+        value = rays_all / (dev_ms * 1e-3) / 1e6
+        # roofline of the render kernel on THIS rank: algorithmic bytes per launch / mean launch time
+        k_ms = kernel_ms / args.steps
+        achieved = (rays / args.steps) * BYTES_PER_RAY / (k_ms * 1e-3) / 1e9
+        line = base_line(args, world)
+        line.update({
+            "value": value, "ms_per_step": dev_ms / args.steps,
+            "e2e": {"value": e_rays_all / e_secs / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * e_secs / args.steps,
+                    "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(rows * WIDTH * 24)},
+            "gpu_launches": launches_all,
+            "rays_per_frame": rays_all / args.steps,
+            "kernel_ms": k_ms,
+            "wall_s_timed_region": wall,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
+                         "model": "%d algorithmic B/ray (SURVEY.md 8d) x rays per launch / CUDA-event launch time; the "
+                                  "working set is L2-resident, so this is a node-fetch figure against the HBM peak" % BYTES_PER_RAY},
+            "clocks": sampler.summary(),
+            "scene_setup": {"parse_flatten_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "blob_bytes": len(blob)},
+        })
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            r, s, desc = cpu_sample(threads)
+            line["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                                    "sample": desc}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ctypes_sizeof_camera(pkg):
+    import ctypes
+    return ctypes.sizeof(pkg.rtc_camera)
+
+
+if __name__ == "__main__":
+    main()
