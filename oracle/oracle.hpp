@@ -56,6 +56,7 @@ void sort_intersections(Intersections& xs, size_t from);
 long hit_index(const Intersections& xs, size_t from = 0);
 bool csg_intersection_allowed(CsgOp op, bool lhit, bool inl, bool inr);
 bool csg_includes(const Shape& a, const Shape& b);
+void csg_filter(const Shape& csg, Intersections& xs, size_t from);
 
 // patterns / shading
 double noise(double x, double y, double z);

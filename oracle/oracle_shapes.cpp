@@ -205,6 +205,19 @@ bool csg_includes(const Shape& a, const Shape& b) {
     return a.id == b.id;
 }
 
+// Csg.filterIntersections (csg.zig:51-73) on the sorted tail xs[from..]
+void csg_filter(const Shape& csg, Intersections& xs, size_t from) {
+    bool inl = false, inr = false;
+    size_t w = from;
+    for (size_t i = from; i < xs.size(); i++) {
+        bool lhit = csg_includes(*csg.left, *xs[i].object);
+        if (csg_intersection_allowed(csg.op, lhit, inl, inr)) xs[w++] = xs[i];
+        if (lhit) inl = !inl;
+        else inr = !inr;
+    }
+    xs.resize(w);
+}
+
 // shape.zig:313-335 : leaves see the ray in object space, groups / CSG pass it through.
 void intersect(const Shape& s, const Ray& ray, Intersections& out) {
     switch (s.kind) {
@@ -221,15 +234,7 @@ void intersect(const Shape& s, const Ray& ray, Intersections& out) {
             intersect(*s.left, ray, out);
             intersect(*s.right, ray, out);
             sort_intersections(out, from);
-            bool inl = false, inr = false;
-            size_t w = from;
-            for (size_t i = from; i < out.size(); i++) {
-                bool lhit = csg_includes(*s.left, *out[i].object);
-                if (csg_intersection_allowed(s.op, lhit, inl, inr)) out[w++] = out[i];
-                if (lhit) inl = !inl;
-                else inr = !inr;
-            }
-            out.resize(w);
+            csg_filter(s, out, from);
             return;
         }
         default: break;

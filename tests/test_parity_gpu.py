@@ -105,3 +105,28 @@ def test_errors(pkg):
     info = pkg.parse_scene(scenes.default_world(), "")
     with pytest.raises(pkg.RtcError):
         info.camera.render(info.world, max_depth=99)
+
+
+@pytest.mark.parametrize("name", ["smoke", "mesh_smooth"] + scenes.SHIPPED)
+def test_against_committed_golden(pkg, tmp_path, name):
+    """CUDA path vs the committed oracle renders (no oracle code involved on this leg)."""
+    from tests.golden import make_golden
+    g = np.load(os.path.join(scenes.ROOT, "tests", "golden", "oracle_renders.npz"))
+    if name == "smoke":
+        text, assets, (w, h) = scenes.SMOKE_SCENE, "", (96, 64)
+    elif name == "mesh_smooth":
+        scenes.write_mesh_obj(str(tmp_path / "torus.obj"), smooth=True, groups=False)
+        text, assets, (w, h) = scenes.mesh_scene("torus.obj"), str(tmp_path), (90, 60)
+    else:
+        s = scenes.shipped_scene(name)
+        if s is None:
+            pytest.skip("reference assets not staged (assets/_ref)")
+        text, assets, (w, h) = s[0], s[1], make_golden.SIZES[name]
+    info = pkg.parse_scene(text, assets, w, h)
+    c = info.camera.render(info.world)
+    diff = np.abs(c.pixels - g[name]).max(axis=2)
+    assert (diff <= TOL).mean() >= 0.999
+    st = c.stats
+    assert int(st.primary_rays) == int(g[name + "__rays"][0])
+    if (diff <= TOL).all():
+        assert [int(st.shadow_rays), int(st.secondary_rays)] == [int(v) for v in g[name + "__rays"][1:]]
