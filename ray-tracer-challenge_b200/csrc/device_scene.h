@@ -37,6 +37,7 @@ struct DMesh {
     float lo[3], hi[3];  // object-space root box (outward rounded)
     float bound_abs[3];  // max |coordinate| of the root box per axis: scales the f32 slab error bound
     float pad[3];
+    double wmin[3], wmax[3];  // conservative WORLD-space box of the mesh (pre-test before the ray transform)
 };
 static_assert(sizeof(DMesh) % 16 == 0, "DMesh alignment");
 

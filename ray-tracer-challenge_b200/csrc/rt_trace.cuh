@@ -188,18 +188,22 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
 __device__ __forceinline__ void trace_mesh(Query& q, const DScene& S, const DMesh& M, int* stack, int* err) {
     uint32_t flags = M.flags;
     if (q.mode == Q_SHADOW && !(flags & RTC_CASTS_SHADOW)) return;
+    {
+        double tn, tf;  // world-space pre-test: skips the ray transform for instances the ray cannot reach
+        if (!box_range(q, M.wmin, M.wmax, tn, tf) || !range_useful(q, tn, tf)) return;
+    }
     M34 inv = load_m34(S.transforms[M.transform].inverse);
     V3 oo = xf_point(inv, q.o), dd = xf_vec(inv, q.d);
     FRay r;
     r.ox = (float)oo.x, r.oy = (float)oo.y, r.oz = (float)oo.z;
-    r.ix = (float)(1.0 / dd.x), r.iy = (float)(1.0 / dd.y), r.iz = (float)(1.0 / dd.z);
+    // f32 reciprocal of the f32-rounded direction: relative error <= 2^-23, inside the bound below
+    r.ix = 1.0f / (float)dd.x, r.iy = 1.0f / (float)dd.y, r.iz = 1.0f / (float)dd.z;
     // |error| of (b - o) * (1/d) evaluated in f32 is below 2^-21 (|b| + 2|o|) |1/d|  (BVH)
     const float k = 4.76837158e-7f;
     r.ex = fminf(FLT_MAX, k * (M.bound_abs[0] + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
     r.ey = fminf(FLT_MAX, k * (M.bound_abs[1] + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
     r.ez = fminf(FLT_MAX, k * (M.bound_abs[2] + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
-    float t_lo = q.mode == Q_CONTAINERS ? -FLT_MAX : 0.0f;
-    t_lo = q.mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : t_lo;
+    float t_lo = q.mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
     double hi_d = q.mode == Q_CLOSEST ? q.best.t : (q.mode == Q_SHADOW ? q.t_max : q.cont.hit_t);
     float t_hi = __double2float_ru(hi_d);
     float tn;

@@ -24,6 +24,48 @@ void check_index(int64_t v, int64_t n, const char* what, bool allow_neg = false)
     if (v < 0 || v >= n) throw std::runtime_error(std::string("blob: index out of range: ") + what);
 }
 
+// World-space box of a mesh: the 8 corners of its object-space root box taken through the forward
+// matrix (the affine inverse of the stored world->object rows), padded.  Only ever used to SKIP work.
+void mesh_world_box(const rtc_transform& t, DMesh& m) {
+    const double* a = t.inverse;  // rows r: a[4r..4r+2] linear part, a[4r+3] translation
+    double A[3][3] = {{a[0], a[1], a[2]}, {a[4], a[5], a[6]}, {a[8], a[9], a[10]}};
+    double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) - A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                 A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+    bool ok = std::isfinite(det) && det != 0.0;
+    double F[3][3];
+    if (ok) {
+        F[0][0] = (A[1][1] * A[2][2] - A[1][2] * A[2][1]) / det;
+        F[0][1] = (A[0][2] * A[2][1] - A[0][1] * A[2][2]) / det;
+        F[0][2] = (A[0][1] * A[1][2] - A[0][2] * A[1][1]) / det;
+        F[1][0] = (A[1][2] * A[2][0] - A[1][0] * A[2][2]) / det;
+        F[1][1] = (A[0][0] * A[2][2] - A[0][2] * A[2][0]) / det;
+        F[1][2] = (A[0][2] * A[1][0] - A[0][0] * A[1][2]) / det;
+        F[2][0] = (A[1][0] * A[2][1] - A[1][1] * A[2][0]) / det;
+        F[2][1] = (A[0][1] * A[2][0] - A[0][0] * A[2][1]) / det;
+        F[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
+    }
+    for (int k = 0; k < 3; k++) m.wmin[k] = INFINITY, m.wmax[k] = -INFINITY;
+    for (int c = 0; c < 8 && ok; c++) {
+        double p[3] = {(c & 1) ? m.hi[0] : m.lo[0], (c & 2) ? m.hi[1] : m.lo[1], (c & 4) ? m.hi[2] : m.lo[2]};
+        double q[3] = {p[0] - a[3], p[1] - a[7], p[2] - a[11]};  // object = A*world + t  =>  world = F*(object - t)
+        for (int k = 0; k < 3; k++) {
+            double w = F[k][0] * q[0] + F[k][1] * q[1] + F[k][2] * q[2];
+            if (!std::isfinite(w)) ok = false;
+            m.wmin[k] = std::fmin(m.wmin[k], w);
+            m.wmax[k] = std::fmax(m.wmax[k], w);
+        }
+    }
+    for (int k = 0; k < 3; k++) {
+        if (!ok) {
+            m.wmin[k] = -INFINITY, m.wmax[k] = INFINITY;
+        } else {
+            double pad = 1e-6 * (std::fabs(m.wmin[k]) + std::fabs(m.wmax[k]) + (m.wmax[k] - m.wmin[k])) + 1e-9;
+            m.wmin[k] -= pad;
+            m.wmax[k] += pad;
+        }
+    }
+}
+
 struct CsgCompiler {
     const std::vector<rtc_node>& nodes;
     const std::vector<int32_t>& children;
@@ -205,6 +247,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             m.hi[a] = b.hi[a];
             m.bound_abs[a] = std::fmax(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
         }
+        mesh_world_box(hs.transforms[(size_t)m.transform], m);
         int32_t node_base = (int32_t)hs.bvh.size(), tri_base = (int32_t)hs.tris.size();
         for (BvhNode n : b.nodes) {
             if (n.n0 > 0) n.c0 += tri_base;

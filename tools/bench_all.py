@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""Kernel time / Mrays/s of every BASELINE.json config (and optionally all 14 scenes) on one GPU.
+Secondary to bench.py (which is the contract line for dragons 1080p): prints one JSON line per config.
+usage: python tools/bench_all.py [--all] [--reps 5]"""
+import argparse
+import importlib
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tests import scenes  # noqa: E402
+
+CONFIGS = [("fresnel", 600, 600), ("cover", 1920, 1080), ("teapot", 1920, 1080), ("dragons", 1920, 1080),
+           ("csg", 3840, 2160), ("skybox", 3840, 2160)]
+NATIVE = [("cubes", 0, 0), ("cylinders", 0, 0), ("reflection_and_refraction", 0, 0), ("xyz", 0, 0), ("groups", 0, 0),
+          ("nefertiti", 0, 0), ("align_check", 0, 0), ("earth", 0, 0)]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--all", action="store_true")
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    import torch
+    pkg = importlib.import_module("ray-tracer-challenge_b200")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    todo = CONFIGS + (NATIVE if args.all else [])
+    if args.only:
+        todo = [c for c in todo if c[0] in args.only.split(",")]
+    for name, w, h in todo:
+        text, assets = scenes.shipped_scene(name)
+        t0 = time.perf_counter()
+        info = pkg.parse_scene(text, assets, w, h)
+        setup = time.perf_counter() - t0
+        cam = info.camera
+        buf = torch.empty((cam.vsize, cam.hsize, 3), dtype=torch.float64, device="cuda")
+        times, st = [], None
+        for i in range(args.reps + 2):
+            flush.zero_()
+            torch.cuda.synchronize()
+            st = cam.render_device(info.world, buf.data_ptr())
+            if i >= 2:
+                times.append(st.kernel_ms)
+        times.sort()
+        ms = times[len(times) // 2]
+        print(json.dumps({"scene": name, "width": cam.hsize, "height": cam.vsize, "kernel_ms": round(ms, 4),
+                          "min_ms": round(times[0], 4), "rays": st.rays, "Mrays_s": round(st.rays / ms / 1e3, 1),
+                          "primary": st.primary_rays, "shadow": st.shadow_rays, "secondary": st.secondary_rays,
+                          "setup_s": round(setup, 3), "checksum": float(buf.sum().item())}), flush=True)
+        info.world.close()
+
+
+if __name__ == "__main__":
+    main()
