@@ -184,77 +184,93 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
     }
 }
 
+// All meshes of the world for one query, as ONE loop shared by the whole warp ("while-while"
+// traversal): every lane walks inner nodes until it holds a leaf, the warp reconverges, and only
+// then are triangles tested -- so the f64 Möller–Trumbore runs with most lanes active instead of the
+// few that happen to reach a leaf in the same step.  A lane that finishes one mesh moves on to its
+// next candidate mesh inside the same loop, so lanes inside different dragons still share code.
+//   node >= 0        inner BvhNode index
+//   node <  0        leaf: ~node = (first DTri << 3) | count       (count <= 4, first < 2^27)
+//   node == MESH_END this lane's traversal stack is empty: advance to the next mesh
 // stack: this thread's column of the shared-memory traversal stack (stride RTC_BLOCK)
-__device__ __forceinline__ void trace_mesh(Query& q, const DScene& S, const DMesh& M, int* stack, int* err) {
-    uint32_t flags = M.flags;
-    if (q.mode == Q_SHADOW && !(flags & RTC_CASTS_SHADOW)) return;
-    {
-        double tn, tf;  // world-space pre-test: skips the ray transform for instances the ray cannot reach
-        if (!box_range(q, M.wmin, M.wmax, tn, tf) || !range_useful(q, tn, tf)) return;
-    }
-    M34 inv = load_m34(S.transforms[M.transform].inverse);
-    V3 oo = xf_point(inv, q.o), dd = xf_vec(inv, q.d);
-    FRay r;
-    r.ox = (float)oo.x, r.oy = (float)oo.y, r.oz = (float)oo.z;
-    // f32 reciprocal of the f32-rounded direction: relative error <= 2^-23, inside the bound below
-    r.ix = 1.0f / (float)dd.x, r.iy = 1.0f / (float)dd.y, r.iz = 1.0f / (float)dd.z;
-    // |error| of (b - o) * (1/d) evaluated in f32 is below 2^-21 (|b| + 2|o|) |1/d|  (BVH)
-    const float k = 4.76837158e-7f;
-    r.ex = fminf(FLT_MAX, k * (M.bound_abs[0] + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
-    r.ey = fminf(FLT_MAX, k * (M.bound_abs[1] + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
-    r.ez = fminf(FLT_MAX, k * (M.bound_abs[2] + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
-    float t_lo = q.mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
-    double hi_d = q.mode == Q_CLOSEST ? q.best.t : (q.mode == Q_SHADOW ? q.t_max : q.cont.hit_t);
-    float t_hi = __double2float_ru(hi_d);
-    float tn;
-    if (!fbox(r, M.lo[0], M.lo[1], M.lo[2], M.hi[0], M.hi[1], M.hi[2], t_lo, t_hi, tn)) return;
-
-    int sp = 0;
-    int node = M.root;
+#define RTC_MESH_END ((int)0x80000000)
+__device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, int* stack, int* err) {
+    const int mode = q.mode;
+    const float t_lo = mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
+    float t_hi = __double2float_ru(mode == Q_CLOSEST ? q.best.t : (mode == Q_SHADOW ? q.t_max : q.cont.hit_t));
+    int mi = 0, sp = 0, node = RTC_MESH_END;
+    V3 oo = q.o, dd = q.d;
+    FRay r = {};
     for (;;) {
-        const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
-        float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-        int4 ci = __ldg(reinterpret_cast<const int4*>(np + 3));
-        if (q.mode == Q_CLOSEST) t_hi = __double2float_ru(q.best.t);
-        float n0, n1;
-        bool h0 = fbox(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, t_lo, t_hi, n0);
-        bool h1 = fbox(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, t_lo, t_hi, n1);
-        // leaves first (they can shrink t_hi), nearer one first
-        if (h0 && h1 && ci.z > 0 && ci.w > 0 && n1 < n0) {
-            mesh_tris(q, S, ci.y, ci.w, oo, dd, flags);
-            mesh_tris(q, S, ci.x, ci.z, oo, dd, flags);
-            h0 = h1 = false;
-        }
-        if (h0 && ci.z > 0) {
-            mesh_tris(q, S, ci.x, ci.z, oo, dd, flags);
-            h0 = false;
-        }
-        if (h1 && ci.w > 0) {
-            mesh_tris(q, S, ci.y, ci.w, oo, dd, flags);
-            h1 = false;
-        }
-        if (q.mode == Q_SHADOW && q.shadowed) return;
-        if (h0 && h1) {
-            int nearc = ci.x, farc = ci.y;
-            if (n1 < n0) {
-                nearc = ci.y;
-                farc = ci.x;
+        if (node == RTC_MESH_END) {
+            // ---- next mesh whose world box the ray can reach (skips the ray transform otherwise) ----
+            for (; mi < S.n_meshes; mi++) {
+                const DMesh& M = S.meshes[mi];
+                if (mode == Q_SHADOW && !(M.flags & RTC_CASTS_SHADOW)) continue;
+                double tn, tf;
+                if (!box_range(q, M.wmin, M.wmax, tn, tf) || !range_useful(q, tn, tf)) continue;
+                M34 inv = load_m34(S.transforms[M.transform].inverse);
+                oo = xf_point(inv, q.o), dd = xf_vec(inv, q.d);  // ray.zig:30-32, once per mesh
+                r.ox = (float)oo.x, r.oy = (float)oo.y, r.oz = (float)oo.z;
+                // f32 reciprocal of the f32-rounded direction: relative error <= 2^-23, inside the bound below
+                r.ix = 1.0f / (float)dd.x, r.iy = 1.0f / (float)dd.y, r.iz = 1.0f / (float)dd.z;
+                // |error| of (b - o) * (1/d) evaluated in f32 is below 2^-21 (|b| + 2|o|) |1/d|  (BVH)
+                const float k = 4.76837158e-7f;
+                r.ex = fminf(FLT_MAX, k * (M.bound_abs[0] + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
+                r.ey = fminf(FLT_MAX, k * (M.bound_abs[1] + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
+                r.ez = fminf(FLT_MAX, k * (M.bound_abs[2] + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
+                if (mode == Q_CLOSEST) t_hi = __double2float_ru(q.best.t);
+                float tnf;
+                if (!fbox(r, M.lo[0], M.lo[1], M.lo[2], M.hi[0], M.hi[1], M.hi[2], t_lo, t_hi, tnf)) continue;
+                node = M.root;
+                mi++;
+                break;
             }
-            if (sp >= RTC_BVH_STACK) {
-                *err |= ERR_BVH_STACK;
-                return;
+            if (node == RTC_MESH_END) return;
+        }
+        // ---- inner nodes, until this lane holds a leaf or runs out of stack ----------------------
+        while (node >= 0) {
+            const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
+            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
+            int4 ci = __ldg(reinterpret_cast<const int4*>(np + 3));
+            float n0, n1;
+            bool h0 = fbox(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, t_lo, t_hi, n0);
+            bool h1 = fbox(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, t_lo, t_hi, n1);
+            int c0 = ci.z > 0 ? ~((ci.x << 3) | ci.z) : ci.x;
+            int c1 = ci.w > 0 ? ~((ci.y << 3) | ci.w) : ci.y;
+            if (h0 && h1) {
+                bool swap = n1 < n0;  // nearer child first: it can shrink t_hi before the other is opened
+                int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
+                if (sp >= RTC_BVH_STACK) {
+                    *err |= ERR_BVH_STACK;
+                    return;
+                }
+                stack[sp * RTC_BLOCK] = farc;
+                sp++;
+                node = nearc;
+            } else if (h0) {
+                node = c0;
+            } else if (h1) {
+                node = c1;
+            } else if (sp > 0) {
+                sp--;
+                node = stack[sp * RTC_BLOCK];
+            } else {
+                node = RTC_MESH_END;
             }
-            stack[sp * RTC_BLOCK] = farc;
-            sp++;
-            node = nearc;
-        } else if (h0) {
-            node = ci.x;
-        } else if (h1) {
-            node = ci.y;
-        } else {
-            if (sp == 0) return;
-            sp--;
-            node = stack[sp * RTC_BLOCK];
+        }
+        // ---- leaf: the reference's triangle test on every record of the leaf --------------------
+        if (node != RTC_MESH_END) {
+            int enc = ~node;
+            mesh_tris(q, S, enc >> 3, enc & 7, oo, dd, 0);
+            if (mode == Q_SHADOW && q.shadowed) return;
+            if (mode == Q_CLOSEST) t_hi = __double2float_ru(q.best.t);
+            if (sp > 0) {
+                sp--;
+                node = stack[sp * RTC_BLOCK];
+            } else {
+                node = RTC_MESH_END;
+            }
         }
     }
 }
@@ -387,9 +403,9 @@ __device__ __forceinline__ void trace(Query& q, const DScene& S, int* stack, int
     for (int i = 0; i < S.n_prims; i++) {
         trace_prim(q, S, __ldg(S.prims + i));
     }
-    for (int i = 0; i < S.n_meshes; i++) {
+    if (S.n_meshes > 0) {
         if (q.mode == Q_SHADOW && q.shadowed) return;
-        trace_mesh(q, S, S.meshes[i], stack, err);
+        trace_meshes(q, S, stack, err);
     }
     for (int i = 0; i < S.n_csg; i++) {
         if (q.mode == Q_SHADOW && q.shadowed) return;

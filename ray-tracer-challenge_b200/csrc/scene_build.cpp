@@ -261,6 +261,9 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         if (b.max_depth > hs.bvh_max_depth) hs.bvh_max_depth = b.max_depth;
     }
 
+    // leaves are encoded on the traversal stack as ~((first << 3) | count)  (rt_trace.cuh trace_meshes)
+    if (hs.tris.size() >= (size_t(1) << 27)) throw std::runtime_error("more than 2^27 mesh triangles");
+
     // ---- CSG programs ------------------------------------------------------------------------------
     CsgCompiler cc{hs.nodes, children, hs.csg_prog};
     for (int32_t r : roots) {
