@@ -5,16 +5,25 @@ NVCC ?= nvcc
 # -fmad=false: the reference (Zig, no fast-math) never fuses a*b+c; keeping IEEE mul+add makes t values,
 # tie-breaks and pattern cell decisions bit-identical to it (DESIGN.md "exact arithmetic").
 FMAD ?= false
-NVFLAGS ?= -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=$(FMAD) -Xcompiler -fPIC,-Wall
-SRC := $(CSRC)/render.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
+EXTRA ?=
+NVFLAGS ?= $(EXTRA) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=$(FMAD) -Xcompiler -fPIC,-Wall
+SRC := $(CSRC)/render_mesh.cu $(CSRC)/render_analytic.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
        $(CSRC)/host/scene.cpp $(CSRC)/host/scene_parser.cpp $(CSRC)/host/obj.cpp $(CSRC)/host/images.cpp \
        $(CSRC)/host/flatten.cpp
 HDR := $(wildcard $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh $(CSRC)/host/*.hpp include/*.h)
 
-all: $(PKG)/librtc_b200.so oracle
+OUT ?= $(PKG)/librtc_b200.so
 
-$(PKG)/librtc_b200.so: $(SRC) $(HDR) Makefile
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(SRC) -lz
+all: $(OUT) oracle
+
+# one object per source so that `make -j` compiles the kernel instantiations in parallel
+OBJDIR ?= build/$(notdir $(basename $(OUT)))
+OBJ := $(patsubst $(CSRC)/%,$(OBJDIR)/%.o,$(SRC))
+$(OBJDIR)/%.o: $(CSRC)/% $(HDR) Makefile
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c -o $@ $<
+$(OUT): $(OBJ)
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(OBJ) -lz
 
 oracle:
 	$(MAKE) -C oracle all

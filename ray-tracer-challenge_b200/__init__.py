@@ -17,7 +17,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtc_b200.so")
+# RTC_B200_LIB: an alternative build of the SAME library (kernel tuning experiments, tools/)
+LIB_PATH = os.environ.get("RTC_B200_LIB") or os.path.join(_HERE, "librtc_b200.so")
 _lib = None
 
 RTC_OK, RTC_ERR_INVALID, RTC_ERR_CUDA, RTC_ERR_PARSE, RTC_ERR_CAPACITY = 0, -1, -2, -3, -4

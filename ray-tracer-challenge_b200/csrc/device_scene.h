@@ -37,9 +37,19 @@ struct DMesh {
     float lo[3], hi[3];  // object-space root box (outward rounded)
     float bound_abs[3];  // max |coordinate| of the root box per axis: scales the f32 slab error bound
     float pad[3];
-    double wmin[3], wmax[3];  // conservative WORLD-space box of the mesh (pre-test before the ray transform)
+    float wlo[3], whi[3];  // conservative WORLD-space box of the mesh, f32 rounded outward (pre-test before
+    float pad2[2];         // the ray transform); +-inf when the transform is degenerate
 };
 static_assert(sizeof(DMesh) % 16 == 0, "DMesh alignment");
+
+// Top-level analytic leaf (or stand-alone triangle): conservative f32 WORLD box + the rtc_leaf it
+// guards.  32 bytes = 2 x 16: the box is tested before the 96-byte rtc_leaf is touched.
+struct DPrim {
+    float lo[3], hi[3];  // ignored when RTC_UNBOUNDED is set in flags
+    int32_t leaf;
+    uint32_t flags;  // copy of rtc_leaf.flags
+};
+static_assert(sizeof(DPrim) == 32, "DPrim must be 32 bytes");
 
 // CSG evaluation program (compiled from rtc_node trees): int4 words {op, a, b, c}.
 enum CsgOpcode {
@@ -68,7 +78,7 @@ struct DScene {
     const rtc_triangle* blob_tris;   // original order (CSG operands, guarded triangles)
     const rtc_guard* guards;
     const rtc_node* nodes;
-    const int32_t* prims;  // top-level analytic leaves (and triangles kept out of meshes)
+    const DPrim* prims;  // top-level analytic leaves (and triangles kept out of meshes)
     const DMesh* meshes;
     const BvhNode* bvh;
     const DTri* tris;
@@ -76,6 +86,8 @@ struct DScene {
     const DCsgRoot* csg_roots;
     int32_t n_lights, n_prims, n_meshes, n_csg;
     int32_t n_leaves, bvh_max_depth;
+    float world_abs[3];  // max finite |coordinate| of any world pre-test box per axis (f32 slab error bound)
+    int32_t stack_cap;   // entries per thread of the shared-memory BVH traversal stack (bvh_max_depth + 2)
 };
 
 }  // namespace rtc

@@ -12,6 +12,7 @@
 //   * every trip through the loop each live lane runs exactly ONE world query (closest hit, shadow
 //     any-hit or the containers scan), so lanes in different shading stages still share the
 //     traversal code and the warp stays converged where the time goes.
+#pragma once
 #include <cuda_runtime.h>
 
 #include "render_params.h"
@@ -36,8 +37,14 @@ __device__ __forceinline__ unsigned char quantise(double c) {
     return (unsigned char)t;
 }
 
-__global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParams P) {
-    __shared__ int s_stack[RTC_BVH_STACK * RTC_BLOCK];
+// MESH: the scene has triangle meshes (BVH traversal compiled in; the traversal stack lives in
+// dynamic shared memory).  Scenes without meshes run the instantiation that carries none of it.
+#ifndef RTC_MIN_BLOCKS
+#define RTC_MIN_BLOCKS 3
+#endif
+template <bool MESH>
+__global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScene S, RenderParams P) {
+    extern __shared__ int s_stack[];  // MESH: S.stack_cap x RTC_BLOCK ints, column per thread
     int* stack = s_stack + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -68,12 +75,10 @@ __global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParam
     q.mode = Q_CLOSEST;
     q.o = ro;
     q.d = rd;
-    q.inv_d = rd;
     q.t_max = 0;
     q.best = hit;
     q.shadowed = false;
     q.cont = {0, -1, 0, -1, 0, 0};
-
     for (;;) {
         // ---- refill idle lanes ------------------------------------------------------------------
         unsigned need = __ballot_sync(0xffffffffu, state == ST_IDLE && !done);
@@ -120,6 +125,9 @@ __global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParam
         if (__all_sync(0xffffffffu, done && state == ST_IDLE)) break;
 
         // ---- one world query per live lane --------------------------------------------------------
+        MeshTrav trav;
+        bool busy = false;
+        (void)trav;
         if (state != ST_IDLE) {
             if (state == ST_CLOSEST) {
                 q.mode = Q_CLOSEST;
@@ -149,7 +157,17 @@ __global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParam
                 q.cont.hit_odd = 0;
                 q.cont.hit_last_t = -RTC_INF;
             }
-            trace(q, S, stack, &err);
+            // analytic prims and CSG objects are finished here; meshes are set up in trav
+            busy = trace_begin<MESH>(q, S, trav, &err);
+        }
+        // every mesh through ONE warp-wide traversal loop; the full-mask votes are the points where
+        // the warp reconverges, so inner-node steps and triangle tests each run with all traversing lanes
+        if constexpr (MESH) {
+            while (__any_sync(0xffffffffu, busy)) {
+                if (busy) busy = mesh_inner(q, S, trav, stack, &err);
+                if (!__any_sync(0xffffffffu, busy)) break;
+                if (busy) busy = mesh_leaf(q, S, trav, stack);
+            }
         }
 
         // ---- consume the result -----------------------------------------------------------------------
@@ -327,16 +345,6 @@ __global__ void __launch_bounds__(RTC_BLOCK) render_kernel(DScene S, RenderParam
         atomicAdd(P.counters + 3, n_secondary);
         if (err) atomicOr(P.counters + 4, (unsigned long long)err);
     }
-}
-
-// Host-side launcher used by scene_device.cu
-int launch_render(const DScene& S, const RenderParams& P, int grid, cudaStream_t stream) {
-    render_kernel<<<grid, RTC_BLOCK, 0, stream>>>(S, P);
-    return (int)cudaGetLastError();
-}
-
-int render_kernel_occupancy(int* blocks_per_sm) {
-    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel, RTC_BLOCK, 0);
 }
 
 }  // namespace rtc

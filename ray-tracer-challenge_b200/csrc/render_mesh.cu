@@ -1,0 +1,17 @@
+// Instantiation of the render kernel for scenes WITH triangle meshes (see render_kernel.cuh).
+#include "render_kernel.cuh"
+
+namespace rtc {
+
+int launch_render_mesh(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream) {
+    render_kernel<true><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+    return (int)cudaGetLastError();
+}
+
+int occupancy_render_mesh(int* blocks_per_sm, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel<true>, RTC_BLOCK, smem);
+}
+
+}  // namespace rtc

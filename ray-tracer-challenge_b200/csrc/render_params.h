@@ -6,6 +6,8 @@
 
 namespace rtc {
 
+#define RTC_BLOCK_THREADS 128  // threads per CTA of the render kernels (== RTC_BLOCK in rt_trace.cuh)
+
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)
     unsigned long long hsize, vsize;
     double half_width, half_height, pixel_size;
@@ -24,7 +26,11 @@ struct RenderParams {
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits
 };
 
-int launch_render(const DScene& S, const RenderParams& P, int grid, cudaStream_t stream);
-int render_kernel_occupancy(int* blocks_per_sm);
+// render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
+// smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).
+int launch_render_mesh(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream);
+int launch_render_analytic(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream);
+int occupancy_render_mesh(int* blocks_per_sm, size_t smem);
+int occupancy_render_analytic(int* blocks_per_sm, size_t smem);
 
 }  // namespace rtc

@@ -11,7 +11,7 @@
 
 namespace rtc {
 
-__device__ __constant__ unsigned char c_perm[256] = {
+static __device__ __constant__ unsigned char c_perm[256] = {
     151, 160, 137, 91,  90,  15,  131, 13,  201, 95,  96,  53,  194, 233, 7,   225, 140, 36,  103, 30,  69,  142,
     8,   99,  37,  240, 21,  10,  23,  190, 6,   148, 247, 120, 234, 75,  0,   26,  197, 62,  94,  252, 219, 203,
     117, 35,  11,  32,  57,  177, 33,  88,  237, 149, 56,  87,  174, 20,  125, 136, 171, 168, 68,  175, 74,  165,
@@ -34,7 +34,7 @@ __device__ __forceinline__ double ngrad(int hash, double x, double y, double z) 
     double v = h < 4 ? y : ((h == 12 || h == 14) ? x : z);
     return ((h & 1) == 0 ? u : -u) + ((h & 2) == 0 ? v : -v);
 }
-__device__ __noinline__ double perlin(double x, double y, double z) {  // noise.zig:52-88
+static __device__ __noinline__ double perlin(double x, double y, double z) {  // noise.zig:52-88
     double fx = floor(x), fy = floor(y), fz = floor(z);
     int X = (int)((long long)fx & 255), Y = (int)((long long)fy & 255), Z = (int)((long long)fz & 255);
     x -= fx;
@@ -85,7 +85,7 @@ struct PatTask {
 
 // Returns the pattern colour at object point `op`.  *err is set on a texture lookup out of range
 // or when the explicit stack overflows.
-__device__ __noinline__ V3 pattern_color(const DScene& S, int root, V3 op, int* err) {
+static __device__ __noinline__ V3 pattern_color(const DScene& S, int root, V3 op, int* err) {
     PatTask stack[RTC_PAT_STACK];
     int sp = 0;
     stack[sp++] = {root, op, 1.0};

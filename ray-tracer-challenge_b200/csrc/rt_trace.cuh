@@ -15,7 +15,6 @@
 namespace rtc {
 
 #define RTC_BLOCK 128
-#define RTC_BVH_STACK 64
 #define RTC_CSG_CAP 32
 #define RTC_CSG_SEG 16
 
@@ -69,30 +68,52 @@ struct Containers {
 struct Query {
     int mode;
     V3 o, d;       // world-space ray
-    V3 inv_d;      // 1/d, for the conservative box pre-tests
     double t_max;  // Q_SHADOW: distance to the light
     Hit best;      // Q_CLOSEST result
     bool shadowed; // Q_SHADOW result
     Containers cont;
 };
 
-// Conservative world-space box pre-test (an optimisation the reference does not have; the boxes are
-// supersets, so it only skips work).  Returns the entry/exit parameters.
-__device__ __forceinline__ bool box_range(const Query& q, const double mn[3], const double mx[3], double& tn,
-                                          double& tf) {
-    double ax = (mn[0] - q.o.x) * q.inv_d.x, bx = (mx[0] - q.o.x) * q.inv_d.x;
-    double ay = (mn[1] - q.o.y) * q.inv_d.y, by = (mx[1] - q.o.y) * q.inv_d.y;
-    double az = (mn[2] - q.o.z) * q.inv_d.z, bz = (mx[2] - q.o.z) * q.inv_d.z;
-    tn = fmax(fmin(ax, bx), fmax(fmin(ay, by), fmin(az, bz)));
-    tf = fmin(fmax(ax, bx), fmin(fmax(ay, by), fmax(az, bz)));
-    double slack = 1e-9 * (fabs(tn) + fabs(tf));
-    return !(tn > tf + slack);
+// ---- conservative f32 slab tests ----------------------------------------------------------------------
+// Used for every box that is only an OPTIMISATION (world pre-test boxes of prims and meshes, BVH
+// nodes): the boxes are supersets rounded outward to f32, and the slab interval is widened by a
+// rigorous bound on the f32 evaluation error, so a box the exact ray touches is never culled.
+//   |error of (b - o) * (1/d) in f32|  <  2^-21 (|b| + 2|o|) |1/d|        (BVH)
+// (rounding of o and d to f32, the f32 reciprocal, one subtraction, one multiplication).
+struct FRay {
+    float ox, oy, oz, ix, iy, iz, ex, ey, ez;
+};
+__device__ __forceinline__ float finv(double d) {
+    // d == 0 (or below f32 range) gives +-inf: clamp, so that (b - o) == 0 yields 0 and not NaN
+    return fminf(fmaxf(1.0f / (float)d, -FLT_MAX), FLT_MAX);
 }
-__device__ __forceinline__ bool range_useful(const Query& q, double tn, double tf) {
-    double slack = 1e-9 * (fabs(tn) + fabs(tf)) + 1e-12;
-    if (q.mode == Q_CLOSEST) return !(tf + slack < 0.0) && !(tn - slack > q.best.t);
-    if (q.mode == Q_SHADOW) return !(tf + slack < 0.0) && !(tn - slack > q.t_max);
-    return !(tn - slack > q.cont.hit_t);
+// babs: max |box coordinate| per axis over the boxes this ray will be tested against
+__device__ __forceinline__ FRay make_fray(V3 o, V3 d, float bax, float bay, float baz) {
+    FRay r;
+    r.ox = (float)o.x, r.oy = (float)o.y, r.oz = (float)o.z;
+    r.ix = finv(d.x), r.iy = finv(d.y), r.iz = finv(d.z);
+    const float k = 4.76837158e-7f;  // 2^-21
+    r.ex = fminf(FLT_MAX, k * (bax + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
+    r.ey = fminf(FLT_MAX, k * (bay + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
+    r.ez = fminf(FLT_MAX, k * (baz + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
+    return r;
+}
+__device__ __forceinline__ bool fbox(const FRay& r, float lx, float ly, float lz, float hx, float hy, float hz,
+                                     float t_lo, float t_hi, float& tnear) {
+    float ax = (lx - r.ox) * r.ix, bx = (hx - r.ox) * r.ix;
+    float ay = (ly - r.oy) * r.iy, by = (hy - r.oy) * r.iy;
+    float az = (lz - r.oz) * r.iz, bz = (hz - r.oz) * r.iz;
+    float tn = fmaxf(fmaxf(fminf(ax, bx) - r.ex, fminf(ay, by) - r.ey), fmaxf(fminf(az, bz) - r.ez, t_lo));
+    float tf = fminf(fminf(fmaxf(ax, bx) + r.ex, fmaxf(ay, by) + r.ey), fminf(fmaxf(az, bz) + r.ez, t_hi));
+    tnear = tn;
+    return tn <= tf;
+}
+// The t-range a query still cares about, rounded outward: nothing outside it can change the result.
+__device__ __forceinline__ float query_t_lo(const Query& q) {
+    return q.mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
+}
+__device__ __forceinline__ float query_t_hi(const Query& q) {
+    return __double2float_ru(q.mode == Q_CLOSEST ? q.best.t : (q.mode == Q_SHADOW ? q.t_max : q.cont.hit_t));
 }
 
 __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint32_t flags, int n, const double* ts) {
@@ -113,15 +134,16 @@ __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint
     }
 }
 
-// One analytic leaf or stand-alone triangle at the top level.
-__device__ __forceinline__ void trace_prim(Query& q, const DScene& S, int leaf_id) {
-    const rtc_leaf& L = S.leaves[leaf_id];
-    uint32_t flags = L.flags;
+// One analytic leaf or stand-alone triangle at the top level.  wr: the world ray in f32 form.
+__device__ __forceinline__ void trace_prim(Query& q, const DScene& S, const FRay& wr, int i) {
+    const float4* pp = reinterpret_cast<const float4*>(S.prims + i);
+    float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+    uint32_t flags = __float_as_uint(p1.w);
     if (q.mode == Q_SHADOW && !(flags & RTC_CASTS_SHADOW)) return;
-    if (!(flags & RTC_UNBOUNDED)) {
-        double tn, tf;
-        if (!box_range(q, L.wmin, L.wmax, tn, tf) || !range_useful(q, tn, tf)) return;
-    }
+    float tn;
+    if (!fbox(wr, p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, query_t_lo(q), query_t_hi(q), tn)) return;
+    int leaf_id = __float_as_int(p1.z);
+    const rtc_leaf& L = S.leaves[leaf_id];
     for (int g = L.guard; g >= 0;) {  // group.zig:46-50 for boxes that are not supersets
         const rtc_guard& G = S.guards[g];
         double a, b;
@@ -147,20 +169,6 @@ __device__ __forceinline__ void trace_prim(Query& q, const DScene& S, int leaf_i
 }
 
 // ---- meshes ---------------------------------------------------------------------------------------
-struct FRay {
-    float ox, oy, oz, ix, iy, iz, ex, ey, ez;
-};
-__device__ __forceinline__ bool fbox(const FRay& r, float lx, float ly, float lz, float hx, float hy, float hz,
-                                     float t_lo, float t_hi, float& tnear) {
-    float ax = (lx - r.ox) * r.ix, bx = (hx - r.ox) * r.ix;
-    float ay = (ly - r.oy) * r.iy, by = (hy - r.oy) * r.iy;
-    float az = (lz - r.oz) * r.iz, bz = (hz - r.oz) * r.iz;
-    float tn = fmaxf(fmaxf(fminf(ax, bx) - r.ex, fminf(ay, by) - r.ey), fmaxf(fminf(az, bz) - r.ez, t_lo));
-    float tf = fminf(fminf(fmaxf(ax, bx) + r.ex, fmaxf(ay, by) + r.ey), fminf(fmaxf(az, bz) + r.ez, t_hi));
-    tnear = tn;
-    return tn <= tf;
-}
-
 __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, int count, V3 oo, V3 dd,
                                           uint32_t flags) {
     for (int i = 0; i < count; i++) {
@@ -184,66 +192,92 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
     }
 }
 
-// All meshes of the world for one query, as ONE loop shared by the whole warp ("while-while"
-// traversal): every lane walks inner nodes until it holds a leaf, the warp reconverges, and only
-// then are triangles tested -- so the f64 Möller–Trumbore runs with most lanes active instead of the
-// few that happen to reach a leaf in the same step.  A lane that finishes one mesh moves on to its
-// next candidate mesh inside the same loop, so lanes inside different dragons still share code.
+// Mesh traversal state of one lane.  It lives across trips of the render loop (render.cu): a lane
+// whose query is finished leaves to be shaded and refilled while the others keep their place.
 //   node >= 0        inner BvhNode index
 //   node <  0        leaf: ~node = (first DTri << 3) | count       (count <= 4, first < 2^27)
-//   node == MESH_END this lane's traversal stack is empty: advance to the next mesh
-// stack: this thread's column of the shared-memory traversal stack (stride RTC_BLOCK)
+//   node == MESH_END the traversal stack is empty: advance to the next candidate mesh
 #define RTC_MESH_END ((int)0x80000000)
-__device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, int* stack, int* err) {
-    const int mode = q.mode;
-    const float t_lo = mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
-    float t_hi = __double2float_ru(mode == Q_CLOSEST ? q.best.t : (mode == Q_SHADOW ? q.t_max : q.cont.hit_t));
-    int mi = 0, sp = 0, node = RTC_MESH_END;
-    V3 oo = q.o, dd = q.d;
-    FRay r = {};
+struct MeshTrav {
+    int mbase;      // meshes [mbase, mbase + 32) are described by mask
+    unsigned mask;  // candidate meshes not visited yet
+    int node, sp;
+    float t_hi;
+    V3 oo, dd;  // the ray in the current mesh's object space
+    FRay r;
+};
+
+// Candidate meshes among [mbase, mbase+32): world box reachable within the query's t-range.
+__device__ __forceinline__ unsigned mesh_mask(const Query& q, const DScene& S, const FRay& wr, int mbase) {
+    unsigned mask = 0;
+    float t_lo = query_t_lo(q), t_hi = query_t_hi(q);
+    int n = min(32, S.n_meshes - mbase);
+    for (int i = 0; i < n; i++) {
+        const float4* mp = reinterpret_cast<const float4*>(S.meshes + mbase + i);
+        int4 hd = __ldg(reinterpret_cast<const int4*>(mp));
+        if (q.mode == Q_SHADOW && !((uint32_t)hd.y & RTC_CASTS_SHADOW)) continue;
+        float4 w0 = __ldg(mp + 4), w1 = __ldg(mp + 5);
+        float tn;
+        if (fbox(wr, w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, t_lo, t_hi, tn)) mask |= 1u << i;
+    }
+    return mask;
+}
+
+__device__ __forceinline__ void mesh_begin(const Query& q, const DScene& S, const FRay& wr, MeshTrav& T) {
+    T.mbase = 0;
+    T.mask = mesh_mask(q, S, wr, 0);
+    T.node = RTC_MESH_END;
+    T.sp = 0;
+    T.t_hi = query_t_hi(q);
+}
+
+// The "while-while" traversal, split at the point where the warp must reconverge (render.cu puts a
+// full-mask ballot between the two halves):
+//   mesh_inner  walks inner nodes -- opening the next candidate mesh when the stack runs dry -- until
+//               the lane holds a leaf; returns false when the query has no mesh work left;
+//   mesh_leaf   runs the reference's triangle test on the held leaf and pops the next node.
+// Because the halves alternate warp-wide, the f64 Möller–Trumbore runs with every traversing lane
+// active instead of the few that reach a leaf in the same step; and because all meshes go through
+// this one loop, lanes inside different meshes and at different depths share the code.
+// stack: this thread's column of the shared-memory traversal stack (stride RTC_BLOCK)
+__device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, MeshTrav& T, int* stack, int* err) {
+    const float t_lo = query_t_lo(q);
+    int node = T.node, sp = T.sp;
     for (;;) {
         if (node == RTC_MESH_END) {
-            // ---- next mesh whose world box the ray can reach (skips the ray transform otherwise) ----
-            for (; mi < S.n_meshes; mi++) {
-                const DMesh& M = S.meshes[mi];
-                if (mode == Q_SHADOW && !(M.flags & RTC_CASTS_SHADOW)) continue;
-                double tn, tf;
-                if (!box_range(q, M.wmin, M.wmax, tn, tf) || !range_useful(q, tn, tf)) continue;
-                M34 inv = load_m34(S.transforms[M.transform].inverse);
-                oo = xf_point(inv, q.o), dd = xf_vec(inv, q.d);  // ray.zig:30-32, once per mesh
-                r.ox = (float)oo.x, r.oy = (float)oo.y, r.oz = (float)oo.z;
-                // f32 reciprocal of the f32-rounded direction: relative error <= 2^-23, inside the bound below
-                r.ix = 1.0f / (float)dd.x, r.iy = 1.0f / (float)dd.y, r.iz = 1.0f / (float)dd.z;
-                // |error| of (b - o) * (1/d) evaluated in f32 is below 2^-21 (|b| + 2|o|) |1/d|  (BVH)
-                const float k = 4.76837158e-7f;
-                r.ex = fminf(FLT_MAX, k * (M.bound_abs[0] + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
-                r.ey = fminf(FLT_MAX, k * (M.bound_abs[1] + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
-                r.ez = fminf(FLT_MAX, k * (M.bound_abs[2] + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
-                if (mode == Q_CLOSEST) t_hi = __double2float_ru(q.best.t);
-                float tnf;
-                if (!fbox(r, M.lo[0], M.lo[1], M.lo[2], M.hi[0], M.hi[1], M.hi[2], t_lo, t_hi, tnf)) continue;
-                node = M.root;
-                mi++;
-                break;
+            // ---- next candidate mesh: ray to object space (ray.zig:30-32, once per mesh) ----------
+            if (T.mask == 0) {
+                if (T.mbase + 32 >= S.n_meshes) return false;
+                T.mbase += 32;
+                T.mask = mesh_mask(q, S, make_fray(q.o, q.d, S.world_abs[0], S.world_abs[1], S.world_abs[2]), T.mbase);
+                continue;
             }
-            if (node == RTC_MESH_END) return;
+            int b = __ffs(T.mask) - 1;
+            T.mask &= T.mask - 1;
+            const DMesh& M = S.meshes[T.mbase + b];
+            M34 inv = load_m34(S.transforms[M.transform].inverse);
+            T.oo = xf_point(inv, q.o), T.dd = xf_vec(inv, q.d);
+            T.r = make_fray(T.oo, T.dd, M.bound_abs[0], M.bound_abs[1], M.bound_abs[2]);
+            float tn;
+            if (!fbox(T.r, M.lo[0], M.lo[1], M.lo[2], M.hi[0], M.hi[1], M.hi[2], t_lo, T.t_hi, tn)) continue;
+            node = M.root;
         }
-        // ---- inner nodes, until this lane holds a leaf or runs out of stack ----------------------
+        const float t_hi = T.t_hi;
         while (node >= 0) {
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
             float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
             int4 ci = __ldg(reinterpret_cast<const int4*>(np + 3));
             float n0, n1;
-            bool h0 = fbox(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, t_lo, t_hi, n0);
-            bool h1 = fbox(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, t_lo, t_hi, n1);
+            bool h0 = fbox(T.r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, t_lo, t_hi, n0);
+            bool h1 = fbox(T.r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, t_lo, t_hi, n1);
             int c0 = ci.z > 0 ? ~((ci.x << 3) | ci.z) : ci.x;
             int c1 = ci.w > 0 ? ~((ci.y << 3) | ci.w) : ci.y;
             if (h0 && h1) {
                 bool swap = n1 < n0;  // nearer child first: it can shrink t_hi before the other is opened
                 int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
-                if (sp >= RTC_BVH_STACK) {
+                if (sp >= S.stack_cap) {
                     *err |= ERR_BVH_STACK;
-                    return;
+                    return false;
                 }
                 stack[sp * RTC_BLOCK] = farc;
                 sp++;
@@ -259,20 +293,25 @@ __device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, int* sta
                 node = RTC_MESH_END;
             }
         }
-        // ---- leaf: the reference's triangle test on every record of the leaf --------------------
-        if (node != RTC_MESH_END) {
-            int enc = ~node;
-            mesh_tris(q, S, enc >> 3, enc & 7, oo, dd, 0);
-            if (mode == Q_SHADOW && q.shadowed) return;
-            if (mode == Q_CLOSEST) t_hi = __double2float_ru(q.best.t);
-            if (sp > 0) {
-                sp--;
-                node = stack[sp * RTC_BLOCK];
-            } else {
-                node = RTC_MESH_END;
-            }
-        }
+        if (node != RTC_MESH_END) break;  // holding a leaf
     }
+    T.node = node;
+    T.sp = sp;
+    return true;
+}
+
+__device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T, int* stack) {
+    int enc = ~T.node;
+    mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, 0);
+    if (q.mode == Q_SHADOW && q.shadowed) return false;
+    if (q.mode == Q_CLOSEST) T.t_hi = __double2float_ru(q.best.t);
+    if (T.sp > 0) {
+        T.sp--;
+        T.node = stack[T.sp * RTC_BLOCK];
+    } else {
+        T.node = RTC_MESH_END;
+    }
+    return true;
 }
 
 // ---- CSG ------------------------------------------------------------------------------------------
@@ -285,7 +324,7 @@ __device__ __forceinline__ bool csg_allowed(int op, bool lhit, bool inl, bool in
 
 // Runs the program of one top-level CSG object: Csg.localIntersect (csg.zig:75-96) for the whole
 // subtree.  Leaves the filtered, sorted list in ts/ids and returns its length.
-__device__ __noinline__ int csg_eval(const DScene& S, int pc, V3 o, V3 d, double* ts, int* ids, int* err) {
+static __device__ __noinline__ int csg_eval(const DScene& S, int pc, V3 o, V3 d, double* ts, int* ids, int* err) {
     int seg[RTC_CSG_SEG];
     int nseg = 0, len = 0;
     for (;;) {
@@ -397,20 +436,23 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
     }
 }
 
-// The whole world for one query.
-__device__ __forceinline__ void trace(Query& q, const DScene& S, int* stack, int* err) {
-    q.inv_d = v3(1.0 / q.d.x, 1.0 / q.d.y, 1.0 / q.d.z);
+// Starts one query: analytic prims and CSG objects are finished here; the meshes are set up in T and
+// walked by mesh_step.  Returns true when mesh work remains.
+template <bool MESH>
+__device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav& T, int* err) {
+    FRay wr = make_fray(q.o, q.d, S.world_abs[0], S.world_abs[1], S.world_abs[2]);
     for (int i = 0; i < S.n_prims; i++) {
-        trace_prim(q, S, __ldg(S.prims + i));
-    }
-    if (S.n_meshes > 0) {
-        if (q.mode == Q_SHADOW && q.shadowed) return;
-        trace_meshes(q, S, stack, err);
+        if (q.mode == Q_SHADOW && q.shadowed) return false;
+        trace_prim(q, S, wr, i);
     }
     for (int i = 0; i < S.n_csg; i++) {
-        if (q.mode == Q_SHADOW && q.shadowed) return;
+        if (q.mode == Q_SHADOW && q.shadowed) return false;
         trace_csg(q, S, S.csg_roots[i], err);
     }
+    if constexpr (!MESH) return false;
+    if (S.n_meshes == 0 || (q.mode == Q_SHADOW && q.shadowed)) return false;
+    mesh_begin(q, S, wr, T);
+    return T.mask != 0 || S.n_meshes > 32;
 }
 
 }  // namespace rtc

@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -37,6 +38,7 @@ struct rtc_scene {
     size_t d_frame_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int grid = 0;
+    size_t smem = 0;  // dynamic shared memory per CTA: the BVH traversal stacks
 };
 
 extern "C" {
@@ -90,7 +92,7 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     } catch (const std::exception& e) {
         return fail(RTC_ERR_INVALID, e.what());
     }
-    if (hs.bvh_max_depth >= 64) return fail(RTC_ERR_CAPACITY, "BVH deeper than the traversal stack");
+    if (hs.bvh_max_depth > 190) return fail(RTC_ERR_CAPACITY, "BVH deeper than the traversal stack can be made");
     if (hs.csg_max_segments > 16) return fail(RTC_ERR_CAPACITY, "CSG nesting deeper than the segment stack");
 
     rtc_scene* s = new rtc_scene();
@@ -141,7 +143,7 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     d.blob_tris = (const rtc_triangle*)(b + o_btri);
     d.guards = (const rtc_guard*)(b + o_guard);
     d.nodes = (const rtc_node*)(b + o_node);
-    d.prims = (const int32_t*)(b + o_prim);
+    d.prims = (const DPrim*)(b + o_prim);
     d.meshes = (const DMesh*)(b + o_mesh);
     d.bvh = (const BvhNode*)(b + o_bvh);
     d.tris = (const DTri*)(b + o_tri);
@@ -153,12 +155,16 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     d.n_csg = (int32_t)hs.csg_roots.size();
     d.n_leaves = (int32_t)hs.leaves.size();
     d.bvh_max_depth = hs.bvh_max_depth;
+    for (int a = 0; a < 3; a++) d.world_abs[a] = hs.world_abs[a];
 
     // persistent grid: every SM filled to the kernel's occupancy
     cudaDeviceProp prop;
     if ((e = cudaGetDeviceProperties(&prop, s->device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
     int per_sm = 0;
-    if ((e = (cudaError_t)render_kernel_occupancy(&per_sm)) != cudaSuccess) return bail(e, "occupancy query");
+    d.stack_cap = d.n_meshes > 0 ? hs.bvh_max_depth + 2 : 0;
+    s->smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
+    e = (cudaError_t)(d.n_meshes > 0 ? occupancy_render_mesh(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, 0));
+    if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;
     *out = s;
@@ -196,7 +202,8 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (P.rows == 0) return RTC_OK;
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
-    CUDA_TRY((cudaError_t)launch_render(s->d, P, s->grid, stream));
+    CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_render_mesh(s->d, P, s->grid, s->smem, stream)
+                                             : launch_render_analytic(s->d, P, s->grid, 0, stream)));
     CUDA_TRY(cudaEventRecord(s->ev1, stream));
     unsigned long long c[8];
     CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, stream));

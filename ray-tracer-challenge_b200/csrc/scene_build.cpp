@@ -26,6 +26,17 @@ void check_index(int64_t v, int64_t n, const char* what, bool allow_neg = false)
 
 // World-space box of a mesh: the 8 corners of its object-space root box taken through the forward
 // matrix (the affine inverse of the stored world->object rows), padded.  Only ever used to SKIP work.
+inline float f32_down(double v) {  // largest float <= v
+    float f = (float)v;
+    if ((double)f > v) f = std::nextafterf(f, -INFINITY);
+    return f;
+}
+inline float f32_up(double v) {  // smallest float >= v
+    float f = (float)v;
+    if ((double)f < v) f = std::nextafterf(f, INFINITY);
+    return f;
+}
+
 void mesh_world_box(const rtc_transform& t, DMesh& m) {
     const double* a = t.inverse;  // rows r: a[4r..4r+2] linear part, a[4r+3] translation
     double A[3][3] = {{a[0], a[1], a[2]}, {a[4], a[5], a[6]}, {a[8], a[9], a[10]}};
@@ -44,24 +55,25 @@ void mesh_world_box(const rtc_transform& t, DMesh& m) {
         F[2][1] = (A[0][1] * A[2][0] - A[0][0] * A[2][1]) / det;
         F[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
     }
-    for (int k = 0; k < 3; k++) m.wmin[k] = INFINITY, m.wmax[k] = -INFINITY;
+    double wmin[3], wmax[3];
+    for (int k = 0; k < 3; k++) wmin[k] = INFINITY, wmax[k] = -INFINITY;
     for (int c = 0; c < 8 && ok; c++) {
         double p[3] = {(c & 1) ? m.hi[0] : m.lo[0], (c & 2) ? m.hi[1] : m.lo[1], (c & 4) ? m.hi[2] : m.lo[2]};
         double q[3] = {p[0] - a[3], p[1] - a[7], p[2] - a[11]};  // object = A*world + t  =>  world = F*(object - t)
         for (int k = 0; k < 3; k++) {
             double w = F[k][0] * q[0] + F[k][1] * q[1] + F[k][2] * q[2];
             if (!std::isfinite(w)) ok = false;
-            m.wmin[k] = std::fmin(m.wmin[k], w);
-            m.wmax[k] = std::fmax(m.wmax[k], w);
+            wmin[k] = std::fmin(wmin[k], w);
+            wmax[k] = std::fmax(wmax[k], w);
         }
     }
     for (int k = 0; k < 3; k++) {
         if (!ok) {
-            m.wmin[k] = -INFINITY, m.wmax[k] = INFINITY;
+            m.wlo[k] = -INFINITY, m.whi[k] = INFINITY;
         } else {
-            double pad = 1e-6 * (std::fabs(m.wmin[k]) + std::fabs(m.wmax[k]) + (m.wmax[k] - m.wmin[k])) + 1e-9;
-            m.wmin[k] -= pad;
-            m.wmax[k] += pad;
+            double pad = 1e-6 * (std::fabs(wmin[k]) + std::fabs(wmax[k]) + (wmax[k] - wmin[k])) + 1e-9;
+            m.wlo[k] = f32_down(wmin[k] - pad);
+            m.whi[k] = f32_up(wmax[k] + pad);
         }
     }
 }
@@ -231,7 +243,15 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             d.pad = 0;
             groups[{l.transform, l.flags & RTC_CASTS_SHADOW}].push_back(d);
         } else {
-            hs.prims.push_back((int32_t)i);
+            DPrim p{};
+            p.leaf = (int32_t)i;
+            p.flags = l.flags;
+            for (int a = 0; a < 3; a++) {
+                bool open = (l.flags & RTC_UNBOUNDED) || !(l.wmin[a] <= l.wmax[a]);  // NaN corners: never cull
+                p.lo[a] = open ? -INFINITY : f32_down(l.wmin[a]);
+                p.hi[a] = open ? INFINITY : f32_up(l.wmax[a]);
+            }
+            hs.prims.push_back(p);
         }
     }
     hs.bvh_max_depth = 0;
@@ -260,6 +280,16 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         hs.meshes.push_back(m);
         if (b.max_depth > hs.bvh_max_depth) hs.bvh_max_depth = b.max_depth;
     }
+
+    // scale of the f32 slab-test error bound for the world-space pre-tests (rt_trace.cuh make_fray)
+    auto note_abs = [&](const float lo[3], const float hi[3]) {
+        for (int a = 0; a < 3; a++) {
+            if (std::isfinite(lo[a])) hs.world_abs[a] = std::fmax(hs.world_abs[a], std::fabs(lo[a]));
+            if (std::isfinite(hi[a])) hs.world_abs[a] = std::fmax(hs.world_abs[a], std::fabs(hi[a]));
+        }
+    };
+    for (const DPrim& p : hs.prims) note_abs(p.lo, p.hi);
+    for (const DMesh& m : hs.meshes) note_abs(m.wlo, m.whi);
 
     // leaves are encoded on the traversal stack as ~((first << 3) | count)  (rt_trace.cuh trace_meshes)
     if (hs.tris.size() >= (size_t(1) << 27)) throw std::runtime_error("more than 2^27 mesh triangles");

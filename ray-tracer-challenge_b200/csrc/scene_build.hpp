@@ -22,13 +22,14 @@ struct HostScene {
     std::vector<rtc_triangle> blob_tris;
     std::vector<rtc_guard> guards;
     std::vector<rtc_node> nodes;
-    std::vector<int32_t> prims;
+    std::vector<DPrim> prims;
     std::vector<DMesh> meshes;
     std::vector<BvhNode> bvh;
     std::vector<DTri> tris;
     std::vector<int4> csg_prog;
     std::vector<DCsgRoot> csg_roots;
     int bvh_max_depth = 0;
+    float world_abs[3] = {0, 0, 0};
     int csg_max_segments = 0;
 };
 
