@@ -48,6 +48,9 @@ typedef struct rtc_stats {
     float kernel_ms; /* CUDA-event time of the render kernel(s) of this call */
     float pad;
     uint64_t launches; /* kernels launched by this call */
+    /* shadow rays (counted in shadow_rays, as the reference casts them) that were NOT traced because
+     * the light is behind the surface: lighting() returns ambient either way (material.zig:55-63) */
+    uint64_t shadow_rays_culled;
 } rtc_stats;
 
 const char* rtc_last_error(void);

@@ -23,7 +23,7 @@ struct RenderParams {
     unsigned int tiles_x;
     double* out;                   // packed rows of the partition, 3 doubles per pixel
     unsigned char* out8;           // or RGBA8 (NULL when `out` is used)
-    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits
+    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };
 
 // render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.

@@ -79,9 +79,11 @@ struct Query {
 // nodes): the boxes are supersets rounded outward to f32, and the slab interval is widened by a
 // rigorous bound on the f32 evaluation error, so a box the exact ray touches is never culled.
 //   |error of (b - o) * (1/d) in f32|  <  2^-21 (|b| + 2|o|) |1/d|        (BVH)
-// (rounding of o and d to f32, the f32 reciprocal, one subtraction, one multiplication).
+// (rounding of o and d to f32, the f32 reciprocal, the rounded product o*(1/d), one fused multiply-add:
+// together below 2^-22 (|b| + 2|o|) |1/d|; the bound used keeps a factor 2 in hand).
 struct FRay {
-    float ox, oy, oz, ix, iy, iz, ex, ey, ez;
+    float cx, cy, cz;  // -o * (1/d): the slab parameter of plane b is fma(b, 1/d, c)
+    float ix, iy, iz, ex, ey, ez;
 };
 __device__ __forceinline__ float finv(double d) {
     // d == 0 (or below f32 range) gives +-inf: clamp, so that (b - o) == 0 yields 0 and not NaN
@@ -90,19 +92,24 @@ __device__ __forceinline__ float finv(double d) {
 // babs: max |box coordinate| per axis over the boxes this ray will be tested against
 __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float bax, float bay, float baz) {
     FRay r;
-    r.ox = (float)o.x, r.oy = (float)o.y, r.oz = (float)o.z;
+    float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z;
     r.ix = finv(d.x), r.iy = finv(d.y), r.iz = finv(d.z);
+    // finite by construction when o is (|1/d| <= FLT_MAX); an overflowing product saturates, and the
+    // error term below is then FLT_MAX too, which leaves that axis unconstrained
+    r.cx = fminf(fmaxf(-ox * r.ix, -FLT_MAX), FLT_MAX);
+    r.cy = fminf(fmaxf(-oy * r.iy, -FLT_MAX), FLT_MAX);
+    r.cz = fminf(fmaxf(-oz * r.iz, -FLT_MAX), FLT_MAX);
     const float k = 4.76837158e-7f;  // 2^-21
-    r.ex = fminf(FLT_MAX, k * (bax + 2.0f * fabsf(r.ox)) * fabsf(r.ix));
-    r.ey = fminf(FLT_MAX, k * (bay + 2.0f * fabsf(r.oy)) * fabsf(r.iy));
-    r.ez = fminf(FLT_MAX, k * (baz + 2.0f * fabsf(r.oz)) * fabsf(r.iz));
+    r.ex = fminf(FLT_MAX, k * (bax + 2.0f * fabsf(ox)) * fabsf(r.ix));
+    r.ey = fminf(FLT_MAX, k * (bay + 2.0f * fabsf(oy)) * fabsf(r.iy));
+    r.ez = fminf(FLT_MAX, k * (baz + 2.0f * fabsf(oz)) * fabsf(r.iz));
     return r;
 }
 __device__ __forceinline__ bool fbox(const FRay& r, float lx, float ly, float lz, float hx, float hy, float hz,
                                      float t_lo, float t_hi, float& tnear) {
-    float ax = (lx - r.ox) * r.ix, bx = (hx - r.ox) * r.ix;
-    float ay = (ly - r.oy) * r.iy, by = (hy - r.oy) * r.iy;
-    float az = (lz - r.oz) * r.iz, bz = (hz - r.oz) * r.iz;
+    float ax = __fmaf_rn(lx, r.ix, r.cx), bx = __fmaf_rn(hx, r.ix, r.cx);
+    float ay = __fmaf_rn(ly, r.iy, r.cy), by = __fmaf_rn(hy, r.iy, r.cy);
+    float az = __fmaf_rn(lz, r.iz, r.cz), bz = __fmaf_rn(hz, r.iz, r.cz);
     float tn = fmaxf(fmaxf(fminf(ax, bx) - r.ex, fminf(ay, by) - r.ey), fmaxf(fminf(az, bz) - r.ez, t_lo));
     float tf = fminf(fminf(fmaxf(ax, bx) + r.ex, fmaxf(ay, by) + r.ey), fminf(fmaxf(az, bz) + r.ez, t_hi));
     tnear = tn;

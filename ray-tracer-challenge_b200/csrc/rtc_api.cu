@@ -217,6 +217,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         stats->pixels = P.rows * cam->hsize;
         stats->kernel_ms = ms;
         stats->launches = 1;
+        stats->shadow_rays_culled = c[5];
     }
     if (c[4]) {
         char buf[160];

@@ -49,7 +49,7 @@ def main():
         ms = times[len(times) // 2]
         print(json.dumps({"scene": name, "width": cam.hsize, "height": cam.vsize, "kernel_ms": round(ms, 4),
                           "min_ms": round(times[0], 4), "rays": st.rays, "Mrays_s": round(st.rays / ms / 1e3, 1),
-                          "primary": st.primary_rays, "shadow": st.shadow_rays, "secondary": st.secondary_rays,
+                          "primary": st.primary_rays, "shadow": st.shadow_rays, "secondary": st.secondary_rays, "shadow_culled": st.shadow_rays_culled,
                           "setup_s": round(setup, 3), "checksum": float(buf.sum().item())}), flush=True)
         info.world.close()
 

@@ -17,6 +17,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "ray-tracer-challenge_b200", "librtc_b200.so")
 
 
+BY = "inner"
+
+
 def line_table(kernel_substr):
     """offset -> (file, line) for the first kernel whose mangled name contains kernel_substr."""
     tmp = tempfile.mkdtemp()
@@ -25,8 +28,8 @@ def line_table(kernel_substr):
     for f in sorted(os.listdir(tmp)):
         if not f.endswith(".cubin"):
             continue
-        out = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
-        cur, infunc = None, False
+        out = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
+        cur, infunc, chain, fresh = None, False, [], True
         for ln in out.splitlines():
             m = re.match(r"\s*\.text\.(\S+):", ln)
             if m:
@@ -36,10 +39,15 @@ def line_table(kernel_substr):
                 continue
             m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
             if m:
-                cur = (os.path.basename(m.group(1)), int(m.group(2)))
+                if fresh:  # first line-info comment after an instruction starts a new inline chain
+                    chain, fresh = [], False
+                chain.append((os.path.basename(m.group(1)), int(m.group(2))))
                 continue
             m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*)", ln)
-            if m and cur:
+            if m and chain:
+                fresh = True
+                cur = chain[0] if BY == "inner" else (chain[-1] if BY == "outer" else
+                                                      (" < ".join("%s:%d" % c for c in chain), 0))
                 table[int(m.group(1), 16)] = (cur, m.group(2).strip())
         if table:
             break
@@ -52,7 +60,11 @@ def main():
     ap.add_argument("--top", type=int, default=40)
     ap.add_argument("--kernel", default="render_kernel")
     ap.add_argument("--sass", action="store_true", help="print the hottest SASS instructions too")
+    ap.add_argument("--by", default="inner", choices=["inner", "outer", "chain"],
+                    help="attribute an instruction to its innermost inlined line, the outermost (kernel) line, or the chain")
     a = ap.parse_args()
+    global BY
+    BY = a.by
     out = subprocess.run(["ncu", "-i", a.rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
@@ -89,7 +101,7 @@ def main():
         print("  %-20s samples %5.1f%%  inst %5.1f%%" % (f, 100.0 * g[0] / max(1, tot_s), 100.0 * g[1] / max(1, tot_i)))
     print("%-28s %8s %8s %8s %8s" % ("source line", "samp%", "inst%", "thr/inst", "noinst%"))
     for (f, l), g in sorted(agg.items(), key=lambda kv: -kv[1][0])[: a.top]:
-        print("%-28s %8.2f %8.2f %8.1f %8.1f" % ("%s:%d" % (f, l), 100.0 * g[0] / max(1, tot_s), 100.0 * g[1] / max(1, tot_i),
+        print("%-28s %8.2f %8.2f %8.1f %8.1f" % (("%s:%d" % (f, l)) if l else f, 100.0 * g[0] / max(1, tot_s), 100.0 * g[1] / max(1, tot_i),
                                                   g[2] / max(1, g[1]), 100.0 * g[3] / max(1, g[0])))
     if a.sass:
         for s, i, key, sass in sorted(hot, key=lambda t: -t[0])[: a.top]:
