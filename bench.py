@@ -42,6 +42,17 @@ def scene_source():
     return s
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one render_kernel launch of THIS workload, from the
+    committed `ncu --set full` capture (profiles/traffic.json, written by profiles/summarize_ncu.py)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return float(t["dram_bytes_per_launch"]), t.get("source", "")
+    except Exception:
+        return None, ""
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -51,34 +62,60 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks + throttle reasons, sampled while the timed region runs."""
+    """SM clock + throttle reasons sampled WHILE the timed region runs (NVML, ~1 kHz; falls back to
+    nvidia-smi, ~20 Hz, when pynvml is missing)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+
+    def sample_nvml(self):
+        nv = self.nv
+        self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                          ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def sample_smi(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        f = [x.strip() for x in out.strip().split(",")]
+        self.samples.append(float(f[0]))
+        self.max_mhz = float(f[1])
+        for n, v in zip(names, f[2:6]):
+            if v.lower().startswith("active"):
+                self.reasons.add(n)
 
     def run(self):
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                self.samples.append(float(f[0]))
-                self.max_mhz = float(f[1])
-                for n, v in zip(names, f[2:6]):
-                    if v.lower().startswith("active"):
-                        self.reasons.add(n)
+                if self.h is not None:
+                    self.sample_nvml()
+                else:
+                    self.sample_smi()
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.001 if self.h is not None else 0.05)
 
     def summary(self):
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "source": "nvml" if self.h is not None else "nvidia-smi"}
 
 
 def cpu_sample(threads, bands=8, frac=0.125):
@@ -132,10 +169,12 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "gather"],
+                    help="N > 1: how the framebuffer reaches rank 0")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -164,26 +203,38 @@ def main():
     camera = pkg.Camera(cam)
     part = (TILE_ROWS, rank, world)
     rows = camera.partition_rows(part)
-    max_rows = max(camera.partition_rows((TILE_ROWS, r, world)) for r in range(world))
-    d_rows = torch.zeros((max_rows, WIDTH, 3), dtype=torch.float64, device=dev)   # this rank's packed rows
-    gathered = [torch.zeros_like(d_rows) for _ in range(world)] if (world > 1 and rank == 0) else None
-    frame = torch.zeros((HEIGHT, WIDTH, 3), dtype=torch.float64, device=dev) if rank == 0 else None
+    mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    # row index of every packed row of every rank, for the de-interleave on rank 0
-    row_maps = []
-    for r in range(world):
-        ys = [y for y in range(HEIGHT) if (y // TILE_ROWS) % world == r]
-        row_maps.append(torch.tensor(ys, dtype=torch.long, device=dev))
+    # N > 1: every rank's kernel stores its tiles straight into rank 0's canvas over NVLink (PeerFrame);
+    # if symmetric memory cannot be set up on this box, packed rows + one NCCL gather (GatherFrame).
+    peer = gather = None
+    exchange = "none (1 GPU)"
+    if world > 1 and args.exchange != "gather":
+        try:
+            peer = mg.PeerFrame(WIDTH, HEIGHT, rank, world, dev)
+            exchange = "peer stores into rank 0's frame (symmetric memory over NVLink) + device barrier"
+        except Exception as e:  # noqa: BLE001
+            if args.exchange == "peer":
+                raise
+            if rank == 0:
+                print("bench: symmetric memory unavailable (%s); falling back to NCCL gather" % e, file=sys.stderr)
+    if peer is None:
+        gather = mg.GatherFrame(WIDTH, HEIGHT, TILE_ROWS, rank, world, dev)
+        if world > 1:
+            exchange = "packed rows + NCCL gather to rank 0 + de-interleave"
 
     def step_device():
-        st = camera.render_device(wld, d_rows.data_ptr(), DEPTH, part, stream)
-        if world > 1:
-            dist.gather(d_rows, gathered, dst=0)
-            if rank == 0:
-                for r in range(world):
-                    frame.index_copy_(0, row_maps[r], gathered[r][: len(row_maps[r])])
+        if peer is not None:
+            st = camera.render_device_frame(wld, peer.root_ptr, DEPTH, part, stream)
+            peer.finish()
+            return st
+        st = camera.render_device(wld, gather.local_ptr(), DEPTH, part, stream)
+        gather.assemble()
         return st
+
+    def frame_on_rank0():
+        return peer.frame if peer is not None else gather.frame
 
     host = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
 
@@ -194,7 +245,7 @@ def main():
             return camera.render(wld, DEPTH, None, out=host).stats
         st = step_device()  # N > 1: render + NCCL gather, then the assembled frame goes to the host on rank 0
         if rank == 0:
-            pinned.copy_(frame, non_blocking=False)
+            pinned.copy_(frame_on_rank0(), non_blocking=False)
         return st
 
     def barrier():
@@ -208,7 +259,7 @@ def main():
     sampler = ClockSampler(local_rank)
     sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    rays = kernel_ms = 0
+    rays = kernel_ms = culled = 0
     launches = 0
     wall0 = time.perf_counter()
     for i in range(args.steps):
@@ -218,6 +269,7 @@ def main():
         st = step_device()
         ev[i][1].record()
         rays += st.rays
+        culled += st.shadow_rays_culled
         kernel_ms += st.kernel_ms
         launches += st.launches
     barrier()
@@ -250,20 +302,25 @@ def main():
         # roofline of the render kernel on THIS rank: algorithmic bytes per launch / mean launch time
         k_ms = kernel_ms / args.steps
         achieved = (rays / args.steps) * BYTES_PER_RAY / (k_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic()
         line = base_line(args, world)
         line.update({
             "value": value, "ms_per_step": dev_ms / args.steps,
             "e2e": {"value": e_rays_all / e_secs / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * e_secs / args.steps,
-                    "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(rows * WIDTH * 24)},
+                    "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24)},
             "gpu_launches": launches_all,
             "rays_per_frame": rays_all / args.steps,
+            # shadow rays the reference casts (and `value` counts) but this renderer does not trace because the
+            # light is behind the surface: the result is ambient either way (material.zig:55-63); rank 0's share
+            "shadow_rays_culled_per_frame": culled / args.steps,
             "kernel_ms": k_ms,
             "wall_s_timed_region": wall,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
                          "model": "%d algorithmic B/ray (SURVEY.md 8d) x rays per launch / CUDA-event launch time; the "
                                   "working set is L2-resident, so this is a node-fetch figure against the HBM peak" % BYTES_PER_RAY},
             "clocks": sampler.summary(),
+            "exchange": exchange,
             "scene_setup": {"parse_flatten_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "blob_bytes": len(blob)},
         })
         if world == 1 and not args.no_cpu_baseline:

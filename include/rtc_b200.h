@@ -75,6 +75,13 @@ int rtc_render_rgba8(rtc_scene* scene, const rtc_camera* cam, int max_depth, con
  * rtc_partition_rows(...) * hsize * 3 doubles.  `stream` is a cudaStream_t (NULL = default). */
 int rtc_render_device(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                       double* d_rgb, void* stream, rtc_stats* stats);
+/* Multi-GPU twin: d_frame is the WHOLE frame (hsize*vsize*3 doubles) and only the rows of `part` are
+ * written, each at its frame position.  d_frame may be memory of ANOTHER GPU mapped into this
+ * device's address space (CUDA peer access / symmetric memory over NVLink): every rank then renders
+ * its interleaved tiles straight into rank 0's canvas and no gather step is needed (camera.zig:116-121:
+ * pixels are independent, so the only exchange of the path is the framebuffer itself). */
+int rtc_render_device_frame(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+                            double* d_frame, void* stream, rtc_stats* stats);
 uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part);
 
 /* Host loader: the C++ mirror of src/parsing (scene.zig:612, obj.zig:195) + flattener, for hosts

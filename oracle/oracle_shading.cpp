@@ -197,7 +197,7 @@ Color lighting(const Material& m, const Light& light, const Shape& object, const
         diffuse = effective.mul(m.diffuse * light_dot_normal);
         Tuple reflectv = lightv.reflect(normal);
         double reflect_dot_eye = reflectv.negate().dot(eyev);
-        if (reflect_dot_eye > 0.0) specular = light.intensity.mul(m.specular * std::pow(reflect_dot_eye, m.shininess));
+        if (reflect_dot_eye > 0.0) specular = light.intensity.mul(m.specular * zig_pow(reflect_dot_eye, m.shininess));
     }
     return ambient.add(diffuse).add(specular);
 }

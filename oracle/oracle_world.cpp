@@ -66,7 +66,7 @@ double schlick(const Comps& c) {
     }
     double frac = (c.n1 - c.n2) / (c.n1 + c.n2);
     double r0 = frac * frac;
-    return r0 + (1.0 - r0) * std::pow(1 - cosv, 5);
+    return r0 + (1.0 - r0) * zig_pow(1 - cosv, 5);
 }
 
 // world.zig:126-154

@@ -25,6 +25,23 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum"]
 
 
+def traffic_json(path, out_path, note):
+    """profiles/traffic.json for bench.py's roofline.traffic: DRAM bytes of ONE launch of the profiled kernel."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    rec = dict(zip(hdr, rows[2]))
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        tot += float(rec[k].replace(",", "")) * scale[units[hdr.index(k)]]
+    with open(out_path, "w") as f:
+        json.dump({"dram_bytes_per_launch": tot, "kernel": rec.get("Kernel Name"),
+                   "source": "ncu --set full, %s, %s" % (path.split("/")[-1], note)}, f, indent=1)
+        f.write("\n")
+
+
 def main(path):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -42,4 +59,7 @@ def main(path):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--traffic":
+        traffic_json(sys.argv[1], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
+    else:
+        main(sys.argv[1])

@@ -56,7 +56,7 @@ class rtc_stats(ctypes.Structure):
 
 # every symbol include/rtc_b200.h declares
 EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
-           "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_partition_rows", "rtc_load_scene_json",
+           "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
            "rtc_blob_free", "rtc_camera_look_at"]
 
 
@@ -80,6 +80,7 @@ def lib():
     L.rtc_render.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_rgba8.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_device.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_render_device_frame.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
     L.rtc_partition_rows.argtypes = [ctypes.c_uint64, ctypes.POINTER(rtc_partition)]
     L.rtc_partition_rows.restype = ctypes.c_uint64
     L.rtc_load_scene_json.argtypes = [cp, cp, ctypes.c_long, ctypes.c_long, ctypes.POINTER(vp),
@@ -215,6 +216,16 @@ class Camera:
         keep, pref = self._part(partition)
         _check(lib().rtc_render_device(world._h, ctypes.byref(self.c), max_depth, pref, ctypes.c_void_p(d_ptr),
                                        ctypes.c_void_p(stream), ctypes.byref(st)))
+        return st
+
+
+    def render_device_frame(self, world, d_frame_ptr, max_depth=5, partition=None, stream=0):
+        """Rows of `partition` written at their positions of a FULL frame at d_frame_ptr (float64 RGB) -- possibly
+        peer-mapped memory of another GPU (multi_gpu.PeerFrame)."""
+        st = rtc_stats()
+        keep, pref = self._part(partition)
+        _check(lib().rtc_render_device_frame(world._h, ctypes.byref(self.c), max_depth, pref,
+                                             ctypes.c_void_p(d_frame_ptr), ctypes.c_void_p(stream), ctypes.byref(st)))
         return st
 
 

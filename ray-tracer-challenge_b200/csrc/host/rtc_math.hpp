@@ -8,6 +8,7 @@
 // The shipped reference binary renders in f64 (src/main.zig:71), so only double exists here.
 #pragma once
 #include <cmath>
+#include <limits>
 #include <cstdint>
 #include <stdexcept>
 
@@ -206,6 +207,75 @@ struct Mat4 : MatN<4> {
 inline double floored_mod(double a, double b) {
     double r = std::fmod(a, b);
     return (a < 0.0) ? std::fmod(r + b, b) : r;
+}
+
+// std.math.pow for f64 as the Zig standard library computes it (lib/std/math/pow.zig, a port of
+// Go's math.Pow; Zig 0.12-dev per build.zig.zon -- the std lib is not vendored in the reference, so
+// this is a restatement of the published algorithm): special cases, then x^yi by squaring on the
+// frexp mantissa with the exponent carried separately, times exp(yf*log(x)) for a fractional part.
+// Call sites: material.zig:69 (specular, y = shininess) and world.zig:288 (schlick, y = 5).
+// For integral y every operation is an exact IEEE multiply / frexp / scalbn, so the device copy
+// (rt_math.cuh zig_pow) returns the same bits.
+inline double zig_pow(double x, double y) {
+    if (y == 0.0 || x == 1.0) return 1.0;
+    if (std::isnan(x) || std::isnan(y)) return std::numeric_limits<double>::quiet_NaN();
+    if (y == 1.0) return x;
+    if (x == 0.0) {
+        bool odd = std::fabs(y) < 9007199254740992.0 && std::fmod(std::fabs(y), 2.0) == 1.0;
+        if (y < 0.0) return odd ? std::copysign(INFINITY, x) : INFINITY;
+        return odd ? x : 0.0;
+    }
+    if (std::isinf(y)) {
+        if (x == -1.0) return 1.0;
+        if ((std::fabs(x) < 1.0) == (y > 0.0)) return 0.0;
+        return INFINITY;
+    }
+    if (std::isinf(x)) {
+        if (x < 0.0) {
+            bool odd = std::fabs(y) < 9007199254740992.0 && std::fmod(std::fabs(y), 2.0) == 1.0;
+            if (y < 0.0) return odd ? -0.0 : 0.0;
+            return odd ? -INFINITY : INFINITY;
+        }
+        return y < 0.0 ? 0.0 : INFINITY;
+    }
+    if (y == 0.5) return std::sqrt(x);
+    if (y == -0.5) return 1.0 / std::sqrt(x);
+    double yi = std::trunc(std::fabs(y));
+    double yf = std::fabs(y) - yi;
+    if (yf != 0.0 && x < 0.0) return std::numeric_limits<double>::quiet_NaN();
+    if (yi >= 9.223372036854775808e18) return std::exp(y * std::log(x));
+    double a1 = 1.0;
+    int ae = 0;
+    if (yf != 0.0) {
+        if (yf > 0.5) {
+            yf -= 1.0;
+            yi += 1.0;
+        }
+        a1 = std::exp(yf * std::log(x));
+    }
+    int xe;
+    double x1 = std::frexp(x, &xe);
+    for (long long i = (long long)yi; i != 0; i >>= 1) {
+        if (xe < -4096 || 4096 < xe) {  // catastrophic over/underflow: the result is 0 or inf either way
+            ae += xe;
+            break;
+        }
+        if (i & 1) {
+            a1 *= x1;
+            ae += xe;
+        }
+        x1 *= x1;
+        xe <<= 1;
+        if (x1 < 0.5) {
+            x1 += x1;
+            xe -= 1;
+        }
+    }
+    if (y < 0.0) {
+        a1 = 1.0 / a1;
+        ae = -ae;
+    }
+    return std::scalbn(a1, ae);
 }
 
 }  // namespace rtc

@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                         rd = normalized(pixel - origin);
                         rw = 1.0;
                         remaining = P.max_depth;
-                        pix = (long long)(pr * P.cam.hsize + px);
+                        pix = (long long)((P.full_frame ? y : pr) * P.cam.hsize + px);
                         pcol = v3(0, 0, 0);
                         rsp = 0;
                         state = ST_CLOSEST;
@@ -165,9 +165,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                 q.cont.hit_odd = 0;
                 q.cont.hit_last_t = -RTC_INF;
             }
-            // analytic prims and CSG objects are finished here; meshes are set up in trav
-            if (!skip) busy = trace_begin<MESH>(q, S, trav, &err);
         }
+        // analytic prims and CSG objects are finished here (warp-wide call); meshes are set up in trav
+        busy = trace_begin<MESH>(q, S, trav, &err, state != ST_IDLE && !skip);
         // every mesh through ONE warp-wide traversal loop; the full-mask votes are the points where
         // the warp reconverges, so inner-node steps and triangle tests each run with all traversing lanes
         if constexpr (MESH) {
@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                     V3 reflectv = lightv - h_normal * (2.0 * dot(lightv, h_normal));  // tuple.zig reflect
                     double rde = dot(neg(reflectv), neg(rd));
                     V3 spec = v3(0, 0, 0);
-                    if (rde > 0.0) spec = li * (M.specular * pow(rde, M.shininess));
+                    if (rde > 0.0) spec = li * (M.specular * zig_pow(rde, M.shininess));
                     sum = sum + diffuse + spec;
                 }
             }
@@ -294,8 +294,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                 } else {
                     double frac = (h_n1 - h_n2) / (h_n1 + h_n2);
                     double r0 = frac * frac;
-                    double x = 1.0 - cosv;
-                    reflectance = r0 + (1.0 - r0) * (x * x * x * x * x);
+                    reflectance = r0 + (1.0 - r0) * zig_pow(1.0 - cosv, 5.0);
                 }
                 refl_w *= reflectance;
                 refr_w *= (1.0 - reflectance);

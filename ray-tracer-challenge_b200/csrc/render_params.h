@@ -6,7 +6,9 @@
 
 namespace rtc {
 
-#define RTC_BLOCK_THREADS 128  // threads per CTA of the render kernels (== RTC_BLOCK in rt_trace.cuh)
+#ifndef RTC_BLOCK_THREADS
+#define RTC_BLOCK_THREADS 128  // threads per CTA of the render kernels
+#endif
 
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)
     unsigned long long hsize, vsize;
@@ -21,7 +23,8 @@ struct RenderParams {
     unsigned long long rows;       // rows of this partition
     unsigned long long n_items;    // tiles_x * tiles_y * 32 work items (some fall outside the frame)
     unsigned int tiles_x;
-    double* out;                   // packed rows of the partition, 3 doubles per pixel
+    int full_frame;                // 0: out holds the packed rows of the partition; 1: the whole frame
+    double* out;                   // 3 doubles per pixel (may be peer-mapped memory of another GPU)
     unsigned char* out8;           // or RGBA8 (NULL when `out` is used)
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };

@@ -65,6 +65,58 @@ __device__ __forceinline__ double zmod(double a, double b) {
 
 #define RTC_INF (__longlong_as_double(0x7ff0000000000000LL))
 
+// std.math.pow(f64) as Zig computes it -- device copy of host/rtc_math.hpp zig_pow (same operations in
+// the same order; for integral y all of them are exact IEEE operations, so the bits match the oracle).
+// Replaces CUDA's general pow(): ~40 instructions on the hot path instead of ~300.
+// Special cases that cannot occur at the two call sites (x is a finite number >= 0) are folded.
+__device__ __forceinline__ double zig_pow(double x, double y) {
+    if (y == 0.0 || x == 1.0) return 1.0;
+    if (isnan(x) || isnan(y)) return __longlong_as_double(0x7ff8000000000000LL);
+    if (y == 1.0) return x;
+    if (x == 0.0) return y < 0.0 ? RTC_INF : 0.0;
+    if (isinf(y)) return ((fabs(x) < 1.0) == (y > 0.0)) ? 0.0 : RTC_INF;
+    if (isinf(x)) return y < 0.0 ? 0.0 : RTC_INF;
+    if (y == 0.5) return sqrt(x);
+    if (y == -0.5) return 1.0 / sqrt(x);
+    double yi = trunc(fabs(y));
+    double yf = fabs(y) - yi;
+    if (yf != 0.0 && x < 0.0) return __longlong_as_double(0x7ff8000000000000LL);
+    if (yi >= 9.223372036854775808e18) return exp(y * log(x));
+    double a1 = 1.0;
+    int ae = 0;
+    if (yf != 0.0) {
+        if (yf > 0.5) {
+            yf -= 1.0;
+            yi += 1.0;
+        }
+        a1 = exp(yf * log(x));
+    }
+    int xe;
+    double x1 = frexp(x, &xe);
+#pragma unroll 1
+    for (long long i = (long long)yi; i != 0; i >>= 1) {
+        if (xe < -4096 || 4096 < xe) {
+            ae += xe;
+            break;
+        }
+        if (i & 1) {
+            a1 *= x1;
+            ae += xe;
+        }
+        x1 *= x1;
+        xe <<= 1;
+        if (x1 < 0.5) {
+            x1 += x1;
+            xe -= 1;
+        }
+    }
+    if (y < 0.0) {
+        a1 = 1.0 / a1;
+        ae = -ae;
+    }
+    return scalbn(a1, ae);
+}
+
 // cube.zig:24-48 == bounding_box.zig:112-136
 __device__ __forceinline__ void check_axis(double origin, double direction, double mn, double mx, double& tmin,
                                            double& tmax) {

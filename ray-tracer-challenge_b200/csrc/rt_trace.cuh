@@ -14,7 +14,8 @@
 
 namespace rtc {
 
-#define RTC_BLOCK 128
+#include "render_params.h"
+#define RTC_BLOCK RTC_BLOCK_THREADS
 #define RTC_CSG_CAP 32
 #define RTC_CSG_SEG 16
 
@@ -141,15 +142,30 @@ __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint
     }
 }
 
-// One analytic leaf or stand-alone triangle at the top level.  wr: the world ray in f32 form.
-__device__ __forceinline__ void trace_prim(Query& q, const DScene& S, const FRay& wr, int i) {
-    const float4* pp = reinterpret_cast<const float4*>(S.prims + i);
-    float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
-    uint32_t flags = __float_as_uint(p1.w);
-    if (q.mode == Q_SHADOW && !(flags & RTC_CASTS_SHADOW)) return;
-    float tn;
-    if (!fbox(wr, p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, query_t_lo(q), query_t_hi(q), tn)) return;
-    int leaf_id = __float_as_int(p1.z);
+// Top-level analytic leaves (and stand-alone triangles), two passes per chunk of 32:
+//   prim_mask   conservative f32 world-box test of every prim -> bit mask (cheap, all lanes in step);
+//   trace_prim  the reference's transform + closed-form intersection of ONE candidate.
+// Each lane then walks its own candidate list, so lanes testing different prims still share the
+// intersection code instead of idling while the warp steps through all prims in order.
+__device__ __forceinline__ unsigned prim_mask(const Query& q, const DScene& S, const FRay& wr, int base) {
+    unsigned mask = 0;
+    const float t_lo = query_t_lo(q), t_hi = query_t_hi(q);
+    const int n = min(32, S.n_prims - base);
+#pragma unroll 1
+    for (int i = 0; i < n; i++) {
+        const float4* pp = reinterpret_cast<const float4*>(S.prims + base + i);
+        float4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+        uint32_t flags = __float_as_uint(p1.w);
+        if (q.mode == Q_SHADOW && !(flags & RTC_CASTS_SHADOW)) continue;
+        float tn;
+        if (fbox(wr, p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, t_lo, t_hi, tn)) mask |= 1u << i;
+    }
+    return mask;
+}
+
+__device__ __forceinline__ void trace_prim(Query& q, const DScene& S, int i) {
+    int leaf_id = S.prims[i].leaf;
+    uint32_t flags = S.prims[i].flags;
     const rtc_leaf& L = S.leaves[leaf_id];
     for (int g = L.guard; g >= 0;) {  // group.zig:46-50 for boxes that are not supersets
         const rtc_guard& G = S.guards[g];
@@ -219,6 +235,7 @@ __device__ __forceinline__ unsigned mesh_mask(const Query& q, const DScene& S, c
     unsigned mask = 0;
     float t_lo = query_t_lo(q), t_hi = query_t_hi(q);
     int n = min(32, S.n_meshes - mbase);
+#pragma unroll 1
     for (int i = 0; i < n; i++) {
         const float4* mp = reinterpret_cast<const float4*>(S.meshes + mbase + i);
         int4 hd = __ldg(reinterpret_cast<const int4*>(mp));
@@ -443,15 +460,25 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
     }
 }
 
-// Starts one query: analytic prims and CSG objects are finished here; the meshes are set up in T and
-// walked by mesh_step.  Returns true when mesh work remains.
+// Starts one query.  Called by ALL 32 lanes of the warp (live = this lane has a query): analytic
+// prims and CSG objects are finished here; the meshes are set up in T and walked by mesh_inner /
+// mesh_leaf.  Returns true when mesh work remains.
+// Prims: each lane's candidate mask is OR-reduced over the warp and the warp steps through the union
+// in prim order -- prims no lane can reach cost nothing, and at every step the participating lanes
+// run the SAME prim (same kind: no divergence inside the intersection switch).
 template <bool MESH>
-__device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav& T, int* err) {
+__device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav& T, int* err, bool live) {
     FRay wr = make_fray(q.o, q.d, S.world_abs[0], S.world_abs[1], S.world_abs[2]);
-    for (int i = 0; i < S.n_prims; i++) {
-        if (q.mode == Q_SHADOW && q.shadowed) return false;
-        trace_prim(q, S, wr, i);
+    for (int base = 0; base < S.n_prims; base += 32) {
+        unsigned mine = live ? prim_mask(q, S, wr, base) : 0u;
+        unsigned todo = __reduce_or_sync(0xffffffffu, mine);
+        while (todo) {
+            int i = __ffs(todo) - 1;
+            todo &= todo - 1;
+            if (((mine >> i) & 1u) && !(q.mode == Q_SHADOW && q.shadowed)) trace_prim(q, S, base + i);
+        }
     }
+    if (!live) return false;
     for (int i = 0; i < S.n_csg; i++) {
         if (q.mode == Q_SHADOW && q.shadowed) return false;
         trace_csg(q, S, S.csg_roots[i], err);

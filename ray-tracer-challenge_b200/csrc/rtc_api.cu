@@ -172,7 +172,7 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
 }
 
 static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
-                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats) {
+                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats, bool full_frame = false) {
     if (!s || !cam) return fail(RTC_ERR_INVALID, "render: NULL scene or camera");
     if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
     if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
@@ -195,6 +195,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.rows = rtc_partition_rows(cam->vsize, part);
     P.tiles_x = (unsigned)((cam->hsize + 7) / 8);
     P.n_items = (unsigned long long)P.tiles_x * ((P.rows + 3) / 4) * 32ull;
+    P.full_frame = full_frame ? 1 : 0;
     P.out = d_rgb;
     P.out8 = d_rgba;
     P.counters = s->d_counters;
@@ -234,6 +235,12 @@ int rtc_render_device(rtc_scene* s, const rtc_camera* cam, int max_depth, const 
                       void* stream, rtc_stats* stats) {
     if (!d_rgb) return fail(RTC_ERR_INVALID, "rtc_render_device: d_rgb is NULL");
     return render_common(s, cam, max_depth, part, d_rgb, nullptr, (cudaStream_t)stream, stats);
+}
+
+int rtc_render_device_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+                            double* d_frame, void* stream, rtc_stats* stats) {
+    if (!d_frame) return fail(RTC_ERR_INVALID, "rtc_render_device_frame: d_frame is NULL");
+    return render_common(s, cam, max_depth, part, d_frame, nullptr, (cudaStream_t)stream, stats, true);
 }
 
 static int ensure_frame(rtc_scene* s, size_t bytes) {

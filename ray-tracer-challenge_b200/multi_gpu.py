@@ -1,0 +1,73 @@
+"""Sharding one frame over the GPUs of a box: one process per GPU (torch.distributed).
+
+Pixels are independent (camera.zig:116-121: each pixel only reads the immutable world), so the frame
+partitions with no collective during rendering.  Rank r renders the interleaved `tile_rows`-row tiles
+r, r+N, r+2N, ... (load balance: neighbouring rows cost about the same).  The only exchange of the path
+is the framebuffer, assembled on rank 0 in one of two ways:
+
+  PeerFrame    rank 0's canvas is symmetric memory mapped into every rank's address space over NVLink;
+               each rank's render kernel stores its pixels straight into it (rtc_render_device_frame), so
+               the "collective" is fused into the kernel's own epilogue and costs one device barrier.
+  GatherFrame  each rank renders packed rows locally, one gather (NCCL on GPUs, gloo on CPU tests) brings
+               them to rank 0, and an index copy de-interleaves them.  Portable fallback, and the
+               host-side logic the CPU tests exercise.
+
+Neither class renders anything itself: both only own buffers and the exchange.
+"""
+import torch
+import torch.distributed as dist
+
+
+def partition_rows(vsize, tile_rows, part, n_parts):
+    """The y's of partition `part`, increasing -- Python mirror of rtc_partition_rows (rtc_api.cu)."""
+    return [y for y in range(vsize) if (y // tile_rows) % n_parts == part]
+
+
+class GatherFrame:
+    """Packed partition rows -> whole frame on rank 0 through one torch.distributed gather."""
+
+    def __init__(self, width, height, tile_rows, rank, world, device, dtype=torch.float64, channels=3):
+        self.rank, self.world, self.device = rank, world, device
+        self.rows = [partition_rows(height, tile_rows, r, world) for r in range(world)]
+        self.max_rows = max(len(r) for r in self.rows)
+        # every rank sends the same shape (gather needs equal sizes); short partitions are padded
+        self.local = torch.zeros((self.max_rows, width, channels), dtype=dtype, device=device)
+        self.frame = torch.zeros((height, width, channels), dtype=dtype, device=device) if rank == 0 else None
+        self.parts = [torch.zeros_like(self.local) for _ in range(world)] if (rank == 0 and world > 1) else None
+        self.index = [torch.tensor(r, dtype=torch.long, device=device) for r in self.rows] if rank == 0 else None
+
+    def local_ptr(self):
+        return self.local.data_ptr()
+
+    def assemble(self):
+        """Call on every rank after rendering into `local`.  Returns the frame on rank 0, None elsewhere."""
+        if self.world > 1:
+            dist.gather(self.local, self.parts, dst=0)
+        if self.rank != 0:
+            return None
+        src = self.parts if self.world > 1 else [self.local]
+        for r in range(self.world):
+            n = len(self.rows[r])
+            if n:
+                self.frame.index_copy_(0, self.index[r], src[r][:n])
+        return self.frame
+
+
+class PeerFrame:
+    """Rank 0's frame as symmetric memory: every rank gets a device pointer to it (NVLink peer mapping)."""
+
+    def __init__(self, width, height, rank, world, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.rank, self.world = rank, world
+        n = height * width * 3
+        self.buf = symm_mem.empty(n, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.frame = self.buf.view(height, width, 3) if rank == 0 else None
+        self.root_ptr = int(self.handle.buffer_ptrs[0])  # rank 0's buffer as THIS device addresses it
+
+    def finish(self):
+        """Device-side barrier on the current stream: when it returns on rank 0's stream, every rank's stores
+        into the frame have been issued and completed."""
+        self.handle.barrier()
+        return self.frame

@@ -1,0 +1,66 @@
+"""Host-side logic of the multi-GPU path on CPU: world_size-2 gloo processes run the same GatherFrame code
+bench.py uses under NCCL (partitioning into interleaved tiles, padding, gather, de-interleave)."""
+import importlib
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, width, height, tile_rows, out_path):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
+        g = mg.GatherFrame(width, height, tile_rows, rank, world, torch.device("cpu"))
+        ys = mg.partition_rows(height, tile_rows, rank, world)
+        # stand-in for the render: row y of the frame holds y + 1 in R, rank in G, x in B
+        for k, y in enumerate(ys):
+            g.local[k, :, 0] = y + 1
+            g.local[k, :, 1] = rank
+            g.local[k, :, 2] = torch.arange(width, dtype=torch.float64)
+        frame = g.assemble()
+        if rank == 0:
+            torch.save(frame, out_path)
+        else:
+            assert frame is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("height,tile_rows", [(37, 8), (16, 8), (5, 8), (64, 1)])
+def test_gather_frame_world2_gloo(tmp_path, height, tile_rows):
+    world, width = 2, 11
+    out = str(tmp_path / "frame.pt")
+    mp.spawn(_worker, args=(world, _free_port(), width, height, tile_rows, out), nprocs=world, join=True)
+    frame = torch.load(out)
+    assert frame.shape == (height, width, 3)
+    for y in range(height):
+        assert torch.all(frame[y, :, 0] == y + 1)
+        assert torch.all(frame[y, :, 1] == (y // tile_rows) % world)
+        assert torch.all(frame[y, :, 2] == torch.arange(width, dtype=torch.float64))
+
+
+def test_partition_rows_matches_c_abi():
+    pkg = importlib.import_module("ray-tracer-challenge_b200")
+    mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
+    cam = pkg.rtc_camera()
+    for vsize in (1, 7, 8, 9, 64, 1080):
+        cam.vsize, cam.hsize = vsize, 4
+        c = pkg.Camera(cam)
+        for n in (1, 2, 3, 8):
+            seen = []
+            for r in range(n):
+                ys = mg.partition_rows(vsize, 8, r, n)
+                assert len(ys) == c.partition_rows((8, r, n))
+                seen += ys
+            assert sorted(seen) == list(range(vsize))  # a partition: every row exactly once

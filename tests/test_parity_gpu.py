@@ -97,6 +97,24 @@ def test_partition_and_rgba8(pkg, oracle):
     assert (np.abs(moved - want).max(axis=2) <= TOL).mean() >= 0.999
 
 
+def test_render_device_frame_partitions(pkg):
+    """Multi-GPU output path on one GPU: every partition rendered straight into ONE full frame (what each rank
+    does into rank 0's peer-mapped canvas) reproduces the whole-frame render bit for bit."""
+    import torch
+    info = pkg.parse_scene(scenes.SMOKE_SCENE, "", 96, 61)  # 61 rows: last tile is ragged
+    full = info.camera.render(info.world)
+    frame = torch.full((61, 96, 3), float("nan"), dtype=torch.float64, device="cuda")
+    rays = 0
+    for part in range(4):
+        st = info.camera.render_device_frame(info.world, frame.data_ptr(), partition=(8, part, 4))
+        rays += st.rays
+    torch.cuda.synchronize()
+    assert np.array_equal(frame.cpu().numpy(), full.pixels)
+    assert rays == full.stats.rays
+    # shadow rays towards a light behind the surface are counted but not traced (material.zig:55-63)
+    assert 0 < full.stats.shadow_rays_culled < full.stats.shadow_rays
+
+
 def test_errors(pkg):
     with pytest.raises(pkg.RtcError):
         pkg.World(b"\0" * 512)
