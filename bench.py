@@ -236,13 +236,16 @@ def main():
     def frame_on_rank0():
         return peer.frame if peer is not None else gather.frame
 
-    host = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
+    # the caller-owned canvas of the e2e leg: page-locked (rtc_host_alloc, what the Zig shim uses), so the kernel
+    # stores pixels straight into host memory; a pageable canvas (staging frame + cudaMemcpy) is timed beside it
+    host = pkg.pinned_empty((HEIGHT, WIDTH, 3))
+    host_pageable = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
 
     pinned = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64).pin_memory() if (world > 1 and rank == 0) else None
 
-    def step_e2e():
+    def step_e2e(canvas=None):
         if world == 1:  # the public call: Camera.render(world) -> host Canvas
-            return camera.render(wld, DEPTH, None, out=host).stats
+            return camera.render(wld, DEPTH, None, out=host if canvas is None else canvas).stats
         st = step_device()  # N > 1: render + NCCL gather, then the assembled frame goes to the host on rank 0
         if rank == 0:
             pinned.copy_(frame_on_rank0(), non_blocking=False)
@@ -285,6 +288,16 @@ def main():
         e_rays += step_e2e().rays
     barrier()
     e_secs = time.perf_counter() - e0
+    p_secs = None
+    if world == 1:
+        step_e2e(host_pageable)
+        barrier()
+        p0 = time.perf_counter()
+        for i in range(args.steps):
+            step_e2e(host_pageable)
+        barrier()
+        p_secs = time.perf_counter() - p0
+        assert np.array_equal(host, host_pageable), "pinned and pageable canvases differ"
     sampler.stop_flag = True
     sampler.join()
 
@@ -307,7 +320,10 @@ def main():
         line.update({
             "value": value, "ms_per_step": dev_ms / args.steps,
             "e2e": {"value": e_rays_all / e_secs / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * e_secs / args.steps,
-                    "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24)},
+                    "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24),
+                    "canvas": "page-locked host memory (rtc_host_alloc): the kernel stores finished pixels into it over "
+                              "PCIe while rendering" if world == 1 else "rank 0 copies the assembled frame to pinned memory",
+                    "pageable_canvas_ms_per_step": (1e3 * p_secs / args.steps) if p_secs else None},
             "gpu_launches": launches_all,
             "rays_per_frame": rays_all / args.steps,
             # shadow rays the reference casts (and `value` counts) but this renderer does not trace because the

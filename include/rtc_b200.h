@@ -67,6 +67,12 @@ void rtc_scene_destroy(rtc_scene* scene);
  * untouched.  max_depth is the `remaining_recursions` seed (5 at camera.zig:118). */
 int rtc_render(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                double* rgb_out, rtc_stats* stats);
+/* Page-locked, device-mapped host memory for canvases.  rtc_render / rtc_render_rgba8 accept any host
+ * pointer; when it comes from rtc_host_alloc (or is otherwise pinned and mapped) rtc_render lets the
+ * kernel write the pixels straight into it over PCIe while it is still rendering, instead of staging the
+ * frame in device memory and copying it afterwards.  The Zig shim allocates its staging canvas here. */
+void* rtc_host_alloc(size_t nbytes);
+void rtc_host_free(void* p);
 /* lib.zig:135-155 twin: clamp()-quantised RGBA8 (color.zig:61-71), alpha 255, 4 bytes per pixel. */
 int rtc_render_rgba8(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                      uint8_t* rgba_out, rtc_stats* stats);

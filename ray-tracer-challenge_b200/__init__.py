@@ -57,7 +57,7 @@ class rtc_stats(ctypes.Structure):
 # every symbol include/rtc_b200.h declares
 EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
-           "rtc_blob_free", "rtc_camera_look_at"]
+           "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free"]
 
 
 def lib():
@@ -87,6 +87,10 @@ def lib():
                                       ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(rtc_camera)]
     L.rtc_blob_free.argtypes = [vp]
     L.rtc_blob_free.restype = None
+    L.rtc_host_alloc.argtypes = [ctypes.c_size_t]
+    L.rtc_host_alloc.restype = vp
+    L.rtc_host_free.argtypes = [vp]
+    L.rtc_host_free.restype = None
     L.rtc_camera_look_at.argtypes = [ctypes.POINTER(rtc_camera)] + [ctypes.POINTER(ctypes.c_double)] * 3
     _lib = L
     return L
@@ -112,6 +116,38 @@ def load_blob(json_text, asset_dir="", width=0, height=0):
     finally:
         L.rtc_blob_free(blob)
     return data, cam
+
+
+class _Pinned:
+    def __init__(self, ptr):
+        self.ptr = ptr
+
+    def __del__(self):
+        try:
+            lib().rtc_host_free(self.ptr)
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype=np.float64):
+    """numpy array in page-locked, device-mapped host memory (rtc_host_alloc).  Camera.render(out=...) into such an
+    array has the kernel write the canvas directly, with no device->host copy after the render."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = lib().rtc_host_alloc(n)
+    if not p:
+        raise RtcError(RTC_ERR_CUDA, lib().rtc_last_error().decode(errors="replace"))
+    owner = _Pinned(p)
+    buf = (ctypes.c_char * n).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+    _PINNED_OWNERS[arr.ctypes.data] = owner  # freed with free_pinned(); numpy cannot own foreign memory
+    return arr
+
+
+_PINNED_OWNERS = {}
+
+
+def free_pinned(arr):
+    _PINNED_OWNERS.pop(arr.ctypes.data, None)
 
 
 class Canvas:

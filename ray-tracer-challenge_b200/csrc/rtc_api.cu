@@ -270,10 +270,43 @@ static int scatter_rows(const rtc_camera* cam, const rtc_partition* part, const 
     return RTC_OK;
 }
 
+// Pinned, device-mapped host memory for canvases (rtc_b200.h).
+void* rtc_host_alloc(size_t nbytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, nbytes ? nbytes : 1, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+        g_error = std::string("rtc_host_alloc: ") + cudaGetErrorString(cudaGetLastError());
+        return nullptr;
+    }
+    return p;
+}
+void rtc_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+// The device-side address of a pinned + mapped host buffer, or NULL for pageable memory.
+static double* mapped_device_pointer(const void* host) {
+    static const bool off = [] {
+        const char* e = std::getenv("RTC_NO_ZEROCOPY");
+        return e && e[0] == '1';
+    }();
+    if (off) return nullptr;
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, host) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
+    return static_cast<double*>(at.devicePointer);
+}
+
 int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* rgb_out,
                rtc_stats* stats) {
     if (!s || !cam || !rgb_out) return fail(RTC_ERR_INVALID, "rtc_render: NULL argument");
     CUDA_TRY(cudaSetDevice(s->device));
+    // Canvas in pinned memory (rtc_host_alloc): the kernel stores every finished pixel straight into it
+    // across PCIe, overlapped with the rendering of the others -- no staging frame, no copy afterwards.
+    if (double* mapped = mapped_device_pointer(rgb_out))
+        return render_common(s, cam, max_depth, part, mapped, nullptr, 0, stats, true);
     uint64_t rows = rtc_partition_rows(cam->vsize, part);
     int rc = ensure_frame(s, (size_t)rows * cam->hsize * 3 * sizeof(double) + 16);
     if (rc) return rc;
