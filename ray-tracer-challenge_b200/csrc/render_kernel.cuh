@@ -37,35 +37,56 @@ __device__ __forceinline__ unsigned char quantise(double c) {
     return (unsigned char)t;
 }
 
-// MESH: the scene has triangle meshes (BVH traversal compiled in; the traversal stack lives in
-// dynamic shared memory).  Scenes without meshes run the instantiation that carries none of it.
+// Per-lane state that is NOT needed while a query is being traced lives in shared memory, one
+// column of doubles per thread (slot k of thread t at park[k * RTC_BLOCK + t]: conflict-free).  The
+// kernel is latency-bound and wants many resident warps, i.e. few registers per thread; with this
+// state in registers ptxas spilled traversal-loop variables to local memory instead (the per-thread
+// frames of a full grid exceed L2: ncu showed 650 MB of DRAM traffic per frame from spills alone).
+enum {
+    PK_RO = 0,       // current ray origin
+    PK_RD = 3,       // current ray direction
+    PK_PCOL = 6,     // colour accumulated for the current pixel
+    PK_NORMAL = 9,   // hit normal (flipped towards the eye)
+    PK_COLOR = 12,   // pattern colour at the hit
+    PK_SURFACE = 15, // sum of lighting() over the lights so far
+    PK_RW = 18,      // product of the reflective / transparency / Schlick factors along the path
+    PK_N1 = 19,
+    PK_N2 = 20,
+    PK_T = 21,       // t of the current hit
+    PK_SLOTS = RTC_PARK_SLOTS
+};
+static_assert(PK_T + 1 == PK_SLOTS, "RTC_PARK_SLOTS (render_params.h) out of date");
+__device__ __forceinline__ V3 pk_ld(const double* pk, int k) {
+    return v3(pk[k * RTC_BLOCK], pk[(k + 1) * RTC_BLOCK], pk[(k + 2) * RTC_BLOCK]);
+}
+__device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
+    pk[k * RTC_BLOCK] = v.x;
+    pk[(k + 1) * RTC_BLOCK] = v.y;
+    pk[(k + 2) * RTC_BLOCK] = v.z;
+}
+#define PK(k) pk[(k) * RTC_BLOCK]
+
+// MESH: the scene has triangle meshes (BVH traversal compiled in; the traversal stacks follow the
+// parked state in dynamic shared memory).  Scenes without meshes run the instantiation without it.
 #ifndef RTC_MIN_BLOCKS
 #define RTC_MIN_BLOCKS 6  // 80 registers: measured best on B200 (latency-bound kernel: occupancy beats spills)
 #endif
 template <bool MESH>
 __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScene S, RenderParams P) {
-    extern __shared__ int s_stack[];  // MESH: S.stack_cap x RTC_BLOCK ints, column per thread
-    int* stack = s_stack + threadIdx.x;
+    extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
+    double* pk = s_mem + threadIdx.x;
+    int* stack = reinterpret_cast<int*>(s_mem + PK_SLOTS * RTC_BLOCK) + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
 
     int state = ST_IDLE;
     bool done = false;
     int err = 0;
-    unsigned long long n_primary = 0, n_shadow = 0, n_secondary = 0, n_culled = 0;
+    unsigned n_primary = 0, n_shadow = 0, n_secondary = 0, n_culled = 0;  // per thread: far below 2^32
 
-    // current ray
-    V3 ro = v3(0, 0, 0), rd = v3(0, 0, 1);
-    double rw = 0.0;
-    int remaining = 0;
-    // current pixel
-    long long pix = -1;
-    V3 pcol = v3(0, 0, 0);
-    // current hit (valid in ST_CONTAINERS / ST_SHADOW)
-    Hit hit = {0, -1, 0, 0};
-    V3 h_point = v3(0, 0, 0), h_normal = v3(0, 0, 0), h_over = v3(0, 0, 0);
-    V3 h_color = v3(0, 0, 0), h_surface = v3(0, 0, 0);
-    double h_n1 = 1.0, h_n2 = 1.0;
+    int remaining = 0;       // recursion budget of the current ray
+    long long pix = -1;      // output index of the current pixel
+    int hit_leaf = -1;       // current hit (valid in ST_CONTAINERS / ST_SHADOW)
     int h_mat = 0, h_light = 0;
 
     RayTask rays[RTC_RAY_STACK];
@@ -73,12 +94,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
 
     Query q;
     q.mode = Q_CLOSEST;
-    q.o = ro;
-    q.d = rd;
-    q.t_max = 0;
-    q.best = hit;
-    q.shadowed = false;
-    q.cont = {0, -1, 0, -1, 0, 0};
+    q.o = v3(0, 0, 0);
+    q.d = v3(0, 0, 1);
+    q.t = 0.0;
+    q.leaf = -1;
+    q.a = q.b = 0.0;
+    q.c_leaf = -1;
+    q.flag = 0;
     for (;;) {
         // ---- refill idle lanes ------------------------------------------------------------------
         unsigned need = __ballot_sync(0xffffffffu, state == ST_IDLE && !done);
@@ -108,12 +130,12 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                         V3 pixel = v3(m[0] * wx + m[1] * wy + m[2] * -1.0 + m[3], m[4] * wx + m[5] * wy + m[6] * -1.0 + m[7],
                                       m[8] * wx + m[9] * wy + m[10] * -1.0 + m[11]);
                         V3 origin = v3(m[3], m[7], m[11]);
-                        ro = origin;
-                        rd = normalized(pixel - origin);
-                        rw = 1.0;
+                        pk_st(pk, PK_RO, origin);
+                        pk_st(pk, PK_RD, normalized(pixel - origin));
+                        PK(PK_RW) = 1.0;
                         remaining = P.max_depth;
                         pix = (long long)((P.full_frame ? y : pr) * P.cam.hsize + px);
-                        pcol = v3(0, 0, 0);
+                        pk_st(pk, PK_PCOL, v3(0, 0, 0));
                         rsp = 0;
                         state = ST_CLOSEST;
                         n_primary++;
@@ -129,41 +151,43 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
         bool busy = false, skip = false;
         (void)trav;
         if (state != ST_IDLE) {
+            q.o = pk_ld(pk, PK_RO);
+            q.d = pk_ld(pk, PK_RD);
             if (state == ST_CLOSEST) {
                 q.mode = Q_CLOSEST;
-                q.o = ro;
-                q.d = rd;
-                q.best.t = RTC_INF;
-                q.best.leaf = -1;
-                q.best.u = q.best.v = 0.0;
+                q.t = RTC_INF;
+                q.leaf = -1;
+                q.a = q.b = 0.0;
             } else if (state == ST_SHADOW) {  // World.isShadowed (world.zig:126-135)
+                // over_point = point + normal * EPSILON, recomputed from the parked ray and hit
+                // (same operations as PreComputations.new, world.zig:219-224: same bits)
+                V3 n = pk_ld(pk, PK_NORMAL);
+                V3 over = (q.o + q.d * PK(PK_T)) + n * 1e-5;
                 const rtc_light& Lg = S.lights[h_light];
-                V3 dir = v3(Lg.position[0], Lg.position[1], Lg.position[2]) - h_over;
+                V3 dir = v3(Lg.position[0], Lg.position[1], Lg.position[2]) - over;
                 double dist = sqrt(dot(dir, dir));
                 q.mode = Q_SHADOW;
-                q.o = h_over;
+                q.o = over;
                 q.d = v3(dir.x / dist, dir.y / dist, dir.z / dist);
-                q.t_max = dist;
-                q.shadowed = false;
+                q.t = dist;
+                q.flag = 0;
                 n_shadow++;
                 // Light behind the surface: lighting() yields ambient whether or not the point is
                 // shadowed (material.zig:55-63: in_shadow -> ambient; light_dot_normal < 0 -> ambient
                 // + black + black), so the ray need not be traced.  Counted, and reported as culled.
-                if (!(dot(q.d, h_normal) >= 0.0)) {
+                if (!(dot(q.d, n) >= 0.0)) {
                     skip = true;
-                    q.shadowed = true;
+                    q.flag = 1;
                     n_culled++;
                 }
             } else {
                 q.mode = Q_CONTAINERS;
-                q.o = ro;
-                q.d = rd;
-                q.cont.hit_t = hit.t;
-                q.cont.hit_leaf = hit.leaf;
-                q.cont.c_t = -RTC_INF;
-                q.cont.c_leaf = -1;
-                q.cont.hit_odd = 0;
-                q.cont.hit_last_t = -RTC_INF;
+                q.t = PK(PK_T);
+                q.leaf = hit_leaf;
+                q.a = -RTC_INF;
+                q.c_leaf = -1;
+                q.flag = 0;
+                q.b = -RTC_INF;
             }
         }
         // analytic prims and CSG objects are finished here (warp-wide call); meshes are set up in trav
@@ -181,17 +205,18 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
         // ---- consume the result -----------------------------------------------------------------------
         bool pop_next = false;
         if (state == ST_CLOSEST) {
-            if (q.best.leaf < 0) {
+            if (q.leaf < 0) {
                 pop_next = true;  // colorAt: no hit -> black (world.zig:119-121)
             } else {
-                // PreComputations.new (world.zig:212-227)
-                hit = q.best;
-                const rtc_leaf& L = S.leaves[hit.leaf];
+                // PreComputations.new (world.zig:212-227); q.o / q.d still hold the ray
+                hit_leaf = q.leaf;
+                PK(PK_T) = q.t;
+                const rtc_leaf& L = S.leaves[hit_leaf];
                 M34 inv = load_m34(S.transforms[L.transform].inverse);
-                h_point = ro + rd * hit.t;
+                V3 point = q.o + q.d * q.t;
                 int kind = L.kind;
-                V3 lp = xf_point(inv, h_point);  // Shape.normalAt (shape.zig:338-350)
-                double u = hit.u, v = hit.v;
+                V3 lp = xf_point(inv, point);  // Shape.normalAt (shape.zig:338-350)
+                double u = q.a, v = q.b;
                 const double* nrm = nullptr;
                 if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
                     nrm = S.normals[L.triangle].n;
@@ -200,40 +225,38 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                         const rtc_triangle& T = S.blob_tris[L.triangle];
                         double tt;
                         tri_intersect(v3(T.p1[0], T.p1[1], T.p1[2]), v3(T.e1[0], T.e1[1], T.e1[2]),
-                                      v3(T.e2[0], T.e2[1], T.e2[2]), xf_point(inv, ro), xf_vec(inv, rd), tt, u, v);
+                                      v3(T.e2[0], T.e2[1], T.e2[2]), xf_point(inv, q.o), xf_vec(inv, q.d), tt, u, v);
                     }
                 }
                 V3 ln = leaf_local_normal(kind, L.minimum, L.maximum, lp, nrm, u, v);
                 V3 n = xf_normal(inv, ln);
-                if (dot(n, neg(rd)) < 0.0) n = neg(n);
-                h_normal = n;
-                h_over = h_point + n * 1e-5;
+                if (dot(n, neg(q.d)) < 0.0) n = neg(n);
+                pk_st(pk, PK_NORMAL, n);
+                V3 over = point + n * 1e-5;
                 h_mat = L.material;
                 const rtc_material& M = S.materials[h_mat];
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
-                h_color = pattern_color(S, M.pattern, xf_point(inv, h_over), &err);
-                h_surface = v3(0, 0, 0);
+                pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
+                pk_st(pk, PK_SURFACE, v3(0, 0, 0));
                 h_light = 0;
-                h_n1 = 1.0;
-                h_n2 = 1.0;
+                PK(PK_N1) = 1.0;
+                PK(PK_N2) = 1.0;
                 // n1/n2 only reach a result through refractedColor / schlick, both gated on
                 // transparency (world.zig:101-102, :178)
                 if (M.transparency != 0.0) state = ST_CONTAINERS;
-                else state = S.n_lights > 0 ? ST_SHADOW : ST_IDLE;
-                if (state == ST_IDLE) state = -1;  // no lights: fall through to the children below
+                else state = S.n_lights > 0 ? ST_SHADOW : -1;  // no lights: straight to the children below
             }
         } else if (state == ST_CONTAINERS) {
-            const Containers& c = q.cont;
-            double ri_hit = S.materials[S.leaves[hit.leaf].material].refractive_index;
-            double ri_c = c.c_leaf >= 0 ? S.materials[S.leaves[c.c_leaf].material].refractive_index : 1.0;
-            if (c.hit_odd) {
-                bool hit_is_last = c.c_leaf < 0 || c.hit_last_t > c.c_t || (c.hit_last_t == c.c_t && hit.leaf > c.c_leaf);
-                h_n1 = hit_is_last ? ri_hit : ri_c;
-                h_n2 = ri_c;
+            double ri_hit = S.materials[S.leaves[hit_leaf].material].refractive_index;
+            double ri_c = q.c_leaf >= 0 ? S.materials[S.leaves[q.c_leaf].material].refractive_index : 1.0;
+            if (q.flag) {  // the hit leaf was a container itself
+                bool hit_is_last = q.c_leaf < 0 || q.b > q.a || (q.b == q.a && hit_leaf > q.c_leaf);
+                PK(PK_N1) = hit_is_last ? ri_hit : ri_c;
+                PK(PK_N2) = ri_c;
             } else {
-                h_n1 = ri_c;
-                h_n2 = ri_hit;
+                PK(PK_N1) = ri_c;
+                PK(PK_N2) = ri_hit;
             }
             state = S.n_lights > 0 ? ST_SHADOW : -1;
         } else if (state == ST_SHADOW) {
@@ -241,21 +264,23 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
             const rtc_light& Lg = S.lights[h_light];
             const rtc_material& M = S.materials[h_mat];
             V3 li = v3(Lg.intensity[0], Lg.intensity[1], Lg.intensity[2]);
-            V3 eff = v3(h_color.x * li.x, h_color.y * li.y, h_color.z * li.z);
+            V3 color = pk_ld(pk, PK_COLOR);
+            V3 eff = v3(color.x * li.x, color.y * li.y, color.z * li.z);
             V3 sum = eff * M.ambient;
-            if (!q.shadowed) {
+            if (!q.flag) {
                 V3 lightv = q.d;  // == normalize(light.position - over_point)
-                double ldn = dot(lightv, h_normal);
+                V3 normal = pk_ld(pk, PK_NORMAL);
+                double ldn = dot(lightv, normal);
                 if (ldn >= 0.0) {
                     V3 diffuse = eff * (M.diffuse * ldn);
-                    V3 reflectv = lightv - h_normal * (2.0 * dot(lightv, h_normal));  // tuple.zig reflect
-                    double rde = dot(neg(reflectv), neg(rd));
+                    V3 reflectv = lightv - normal * (2.0 * dot(lightv, normal));  // tuple.zig reflect
+                    double rde = dot(neg(reflectv), neg(pk_ld(pk, PK_RD)));
                     V3 spec = v3(0, 0, 0);
                     if (rde > 0.0) spec = li * (M.specular * zig_pow(rde, M.shininess));
                     sum = sum + diffuse + spec;
                 }
             }
-            h_surface = h_surface + sum;
+            pk_st(pk, PK_SURFACE, pk_ld(pk, PK_SURFACE) + sum);
             h_light++;
             if (h_light >= S.n_lights) state = -1;
         }
@@ -263,7 +288,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
         if (state == -1) {
             // shadeHit tail (world.zig:97-107) with the children deferred onto the ray stack
             const rtc_material& M = S.materials[h_mat];
-            pcol = pcol + h_surface * rw;
+            const double rw = PK(PK_RW), h_n1 = PK(PK_N1), h_n2 = PK(PK_N2);
+            const V3 ro = pk_ld(pk, PK_RO), rd = pk_ld(pk, PK_RD), h_normal = pk_ld(pk, PK_NORMAL);
+            pk_st(pk, PK_PCOL, pk_ld(pk, PK_PCOL) + pk_ld(pk, PK_SURFACE) * rw);
             V3 eyev = neg(rd);
             double refl_w = 0.0, refr_w = 0.0;
             V3 refr_dir = v3(0, 0, 0);
@@ -299,19 +326,23 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
                 refl_w *= reflectance;
                 refr_w *= (1.0 - reflectance);
             }
-            if (spawn_refr) {
-                V3 under = h_point - h_normal * 1e-5;
-                if (rsp < RTC_RAY_STACK) {
-                    rays[rsp++] = {under.x, under.y, under.z, refr_dir.x, refr_dir.y, refr_dir.z, rw * refr_w, remaining - 1, 0};
+            if (spawn_refr || spawn_refl) {
+                V3 h_point = ro + rd * PK(PK_T);  // world.zig:219
+                if (spawn_refr) {
+                    V3 under = h_point - h_normal * 1e-5;
+                    if (rsp < RTC_RAY_STACK) {
+                        rays[rsp++] = {under.x, under.y, under.z, refr_dir.x, refr_dir.y, refr_dir.z, rw * refr_w, remaining - 1, 0};
+                    }
+                    n_secondary++;
                 }
-                n_secondary++;
-            }
-            if (spawn_refl) {
-                V3 reflectv = rd - h_normal * (2.0 * dot(rd, h_normal));
-                if (rsp < RTC_RAY_STACK) {
-                    rays[rsp++] = {h_over.x, h_over.y, h_over.z, reflectv.x, reflectv.y, reflectv.z, rw * refl_w, remaining - 1, 0};
+                if (spawn_refl) {
+                    V3 h_over = h_point + h_normal * 1e-5;
+                    V3 reflectv = rd - h_normal * (2.0 * dot(rd, h_normal));
+                    if (rsp < RTC_RAY_STACK) {
+                        rays[rsp++] = {h_over.x, h_over.y, h_over.z, reflectv.x, reflectv.y, reflectv.z, rw * refl_w, remaining - 1, 0};
+                    }
+                    n_secondary++;
                 }
-                n_secondary++;
             }
             pop_next = true;
         }
@@ -319,12 +350,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
         if (pop_next) {
             if (rsp > 0) {
                 RayTask tk = rays[--rsp];
-                ro = v3(tk.ox, tk.oy, tk.oz);
-                rd = v3(tk.dx, tk.dy, tk.dz);
-                rw = tk.w;
+                pk_st(pk, PK_RO, v3(tk.ox, tk.oy, tk.oz));
+                pk_st(pk, PK_RD, v3(tk.dx, tk.dy, tk.dz));
+                PK(PK_RW) = tk.w;
                 remaining = tk.remaining;
                 state = ST_CLOSEST;
             } else {
+                V3 pcol = pk_ld(pk, PK_PCOL);
                 if (P.out8) {
                     uchar4 c = make_uchar4(quantise(pcol.x), quantise(pcol.y), quantise(pcol.z), 255);
                     reinterpret_cast<uchar4*>(P.out8)[pix] = c;
@@ -340,18 +372,19 @@ __global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScen
     }
 
     // ---- ray counters: warp reduce, one atomic per warp -------------------------------------------
+    unsigned long long c_primary = n_primary, c_shadow = n_shadow, c_secondary = n_secondary, c_culled = n_culled;
     for (int s = 16; s > 0; s >>= 1) {
-        n_primary += __shfl_down_sync(0xffffffffu, n_primary, s);
-        n_shadow += __shfl_down_sync(0xffffffffu, n_shadow, s);
-        n_secondary += __shfl_down_sync(0xffffffffu, n_secondary, s);
-        n_culled += __shfl_down_sync(0xffffffffu, n_culled, s);
+        c_primary += __shfl_down_sync(0xffffffffu, c_primary, s);
+        c_shadow += __shfl_down_sync(0xffffffffu, c_shadow, s);
+        c_secondary += __shfl_down_sync(0xffffffffu, c_secondary, s);
+        c_culled += __shfl_down_sync(0xffffffffu, c_culled, s);
         err |= __shfl_down_sync(0xffffffffu, err, s);
     }
     if (lane == 0) {
-        atomicAdd(P.counters + 1, n_primary);
-        atomicAdd(P.counters + 2, n_shadow);
-        atomicAdd(P.counters + 3, n_secondary);
-        atomicAdd(P.counters + 5, n_culled);
+        atomicAdd(P.counters + 1, c_primary);
+        atomicAdd(P.counters + 2, c_shadow);
+        atomicAdd(P.counters + 3, c_secondary);
+        atomicAdd(P.counters + 5, c_culled);
         if (err) atomicOr(P.counters + 4, (unsigned long long)err);
     }
 }

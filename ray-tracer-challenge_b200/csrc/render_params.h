@@ -10,6 +10,8 @@ namespace rtc {
 #define RTC_BLOCK_THREADS 128  // threads per CTA of the render kernels
 #endif
 
+#define RTC_PARK_SLOTS 22  // doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*)
+
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)
     unsigned long long hsize, vsize;
     double half_width, half_height, pixel_size;

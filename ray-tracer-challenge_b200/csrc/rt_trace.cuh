@@ -22,58 +22,50 @@ namespace rtc {
 enum { Q_CLOSEST = 0, Q_SHADOW = 1, Q_CONTAINERS = 2 };
 enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8 };
 
-struct Hit {
+// One world query.  The three modes never coexist, so they share their fields:
+//                 t                 leaf        a       b            c_leaf      flag
+//   Q_CLOSEST     best t so far     best leaf   u       v            -           -
+//   Q_SHADOW      light distance    -           -       -            -           shadowed
+//   Q_CONTAINERS  t of the hit      hit leaf    c_t     hit_last_t   c_leaf      hit_odd
+// In every mode nothing beyond t can change the result: t is the far end of the useful range.
+struct Query {
+    int mode;
+    V3 o, d;  // world-space ray
     double t;
     int leaf;  // -1 = none
-    double u, v;
+    double a, b;
+    int c_leaf;
+    int flag;
 };
 
 // The containers walk reduced to a streaming form.  Processing the sorted list up to the hit, an
 // object is in `containers` iff it has an ODD number of intersections before the hit, and it sits
 // at the position of its LAST such intersection (remove-or-append, world.zig:240-249).  So:
 //   last container before the hit = the odd-parity leaf whose last pre-hit intersection has the
-//   greatest (t, leaf order) key; n1 is its refractive index (1.0 if none);
-//   the hit toggles its own leaf: if it was inside (odd) it is removed and n2 comes from the best
-//   OTHER leaf (or stays 1.0: the reference does not break on an empty list), else it is appended
-//   last and n2 is its own index.
-struct Containers {
-    double hit_t;
-    int hit_leaf;
-    double c_t;   // best candidate among leaves other than the hit leaf
-    int c_leaf;   // -1 = none
-    int hit_odd;  // hit leaf has an odd number of intersections before the hit
-    double hit_last_t;
-
-    __device__ __forceinline__ void add(int leaf, int n, const double* ts) {
-        int cnt = 0;
-        double tl = -RTC_INF;
-        for (int i = 0; i < n; i++) {
-            bool before = ts[i] < hit_t || (ts[i] == hit_t && leaf < hit_leaf);
-            if (before) {
-                cnt++;
-                tl = fmax(tl, ts[i]);
-            }
-        }
-        if (cnt & 1) {
-            if (leaf == hit_leaf) {
-                hit_odd = 1;
-                hit_last_t = tl;
-            } else if (c_leaf < 0 || tl > c_t || (tl == c_t && leaf > c_leaf)) {
-                c_t = tl;
-                c_leaf = leaf;
-            }
+//   greatest (t, leaf order) key (kept in q.a / q.c_leaf); n1 is its refractive index (1.0 if none);
+//   the hit toggles its own leaf: if it was inside (odd: q.flag, its last pre-hit t in q.b) it is
+//   removed and n2 comes from the best OTHER leaf (or stays 1.0: the reference does not break on an
+//   empty list), else it is appended last and n2 is its own index.
+__device__ __forceinline__ void cont_add(Query& q, int leaf, int n, const double* ts) {
+    int cnt = 0;
+    double tl = -RTC_INF;
+    for (int i = 0; i < n; i++) {
+        bool before = ts[i] < q.t || (ts[i] == q.t && leaf < q.leaf);
+        if (before) {
+            cnt++;
+            tl = fmax(tl, ts[i]);
         }
     }
-};
-
-struct Query {
-    int mode;
-    V3 o, d;       // world-space ray
-    double t_max;  // Q_SHADOW: distance to the light
-    Hit best;      // Q_CLOSEST result
-    bool shadowed; // Q_SHADOW result
-    Containers cont;
-};
+    if (cnt & 1) {
+        if (leaf == q.leaf) {
+            q.flag = 1;
+            q.b = tl;
+        } else if (q.c_leaf < 0 || tl > q.a || (tl == q.a && leaf > q.c_leaf)) {
+            q.a = tl;
+            q.c_leaf = leaf;
+        }
+    }
+}
 
 // ---- conservative f32 slab tests ----------------------------------------------------------------------
 // Used for every box that is only an OPTIMISATION (world pre-test boxes of prims and meshes, BVH
@@ -121,24 +113,24 @@ __device__ __forceinline__ float query_t_lo(const Query& q) {
     return q.mode == Q_CONTAINERS ? -__int_as_float(0x7f800000) : 0.0f;
 }
 __device__ __forceinline__ float query_t_hi(const Query& q) {
-    return __double2float_ru(q.mode == Q_CLOSEST ? q.best.t : (q.mode == Q_SHADOW ? q.t_max : q.cont.hit_t));
+    return __double2float_ru(q.t);
 }
 
 __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint32_t flags, int n, const double* ts) {
     if (q.mode == Q_CLOSEST) {
         for (int i = 0; i < n; i++) {
             double t = ts[i];
-            if (t >= 0.0 && (t < q.best.t || (t == q.best.t && leaf < q.best.leaf))) {
-                q.best.t = t;
-                q.best.leaf = leaf;
+            if (t >= 0.0 && (t < q.t || (t == q.t && leaf < q.leaf))) {
+                q.t = t;
+                q.leaf = leaf;
             }
         }
     } else if (q.mode == Q_SHADOW) {
         if (flags & RTC_CASTS_SHADOW)
             for (int i = 0; i < n; i++)
-                if (ts[i] >= 0.0 && ts[i] < q.t_max) q.shadowed = true;
+                if (ts[i] >= 0.0 && ts[i] < q.t) q.flag = 1;
     } else {
-        q.cont.add(leaf, n, ts);
+        cont_add(q, leaf, n, ts);
     }
 }
 
@@ -201,16 +193,16 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
         if (!tri_intersect(v3(a.x, a.y, b.x), v3(b.y, c.x, c.y), v3(e.x, e.y, f.x), oo, dd, t, u, v)) continue;
         int leaf = (int)(__double_as_longlong(f.y) & 0xffffffffLL);
         if (q.mode == Q_CLOSEST) {
-            if (t >= 0.0 && (t < q.best.t || (t == q.best.t && leaf < q.best.leaf))) {
-                q.best.t = t;
-                q.best.leaf = leaf;
-                q.best.u = u;
-                q.best.v = v;
+            if (t >= 0.0 && (t < q.t || (t == q.t && leaf < q.leaf))) {
+                q.t = t;
+                q.leaf = leaf;
+                q.a = u;
+                q.b = v;
             }
         } else if (q.mode == Q_SHADOW) {
-            if (t >= 0.0 && t < q.t_max) q.shadowed = true;
+            if (t >= 0.0 && t < q.t) q.flag = 1;
         } else {
-            q.cont.add(leaf, 1, &t);
+            cont_add(q, leaf, 1, &t);
         }
     }
 }
@@ -327,8 +319,8 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
 __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T, int* stack) {
     int enc = ~T.node;
     mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, 0);
-    if (q.mode == Q_SHADOW && q.shadowed) return false;
-    if (q.mode == Q_CLOSEST) T.t_hi = __double2float_ru(q.best.t);
+    if (q.mode == Q_SHADOW && q.flag) return false;
+    if (q.mode == Q_CLOSEST) T.t_hi = __double2float_ru(q.t);
     if (T.sp > 0) {
         T.sp--;
         T.node = stack[T.sp * RTC_BLOCK];
@@ -433,16 +425,16 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
     if (q.mode == Q_CLOSEST) {
         for (int i = 0; i < len; i++) {  // sorted: the first t >= 0 is this object's candidate
             if (ts[i] >= 0.0) {
-                if (ts[i] < q.best.t || (ts[i] == q.best.t && ids[i] < q.best.leaf)) {
-                    q.best.t = ts[i];
-                    q.best.leaf = ids[i];
+                if (ts[i] < q.t || (ts[i] == q.t && ids[i] < q.leaf)) {
+                    q.t = ts[i];
+                    q.leaf = ids[i];
                 }
                 break;
             }
         }
     } else if (q.mode == Q_SHADOW) {
         for (int i = 0; i < len; i++)
-            if (ts[i] >= 0.0 && ts[i] < q.t_max && (S.leaves[ids[i]].flags & RTC_CASTS_SHADOW)) q.shadowed = true;
+            if (ts[i] >= 0.0 && ts[i] < q.t && (S.leaves[ids[i]].flags & RTC_CASTS_SHADOW)) q.flag = 1;
     } else {
         // per-leaf parity over the filtered list: visit each leaf at its first entry
         for (int i = 0; i < len; i++) {
@@ -455,7 +447,7 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
             int n = 0;
             for (int j = i; j < len; j++)
                 if (ids[j] == leaf) lt[n++] = ts[j];
-            q.cont.add(leaf, n, lt);
+            cont_add(q, leaf, n, lt);
         }
     }
 }
@@ -475,16 +467,16 @@ __device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav&
         while (todo) {
             int i = __ffs(todo) - 1;
             todo &= todo - 1;
-            if (((mine >> i) & 1u) && !(q.mode == Q_SHADOW && q.shadowed)) trace_prim(q, S, base + i);
+            if (((mine >> i) & 1u) && !(q.mode == Q_SHADOW && q.flag)) trace_prim(q, S, base + i);
         }
     }
     if (!live) return false;
     for (int i = 0; i < S.n_csg; i++) {
-        if (q.mode == Q_SHADOW && q.shadowed) return false;
+        if (q.mode == Q_SHADOW && q.flag) return false;
         trace_csg(q, S, S.csg_roots[i], err);
     }
     if constexpr (!MESH) return false;
-    if (S.n_meshes == 0 || (q.mode == Q_SHADOW && q.shadowed)) return false;
+    if (S.n_meshes == 0 || (q.mode == Q_SHADOW && q.flag)) return false;
     mesh_begin(q, S, wr, T);
     return T.mask != 0 || S.n_meshes > 32;
 }

@@ -162,8 +162,10 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if ((e = cudaGetDeviceProperties(&prop, s->device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
     int per_sm = 0;
     d.stack_cap = d.n_meshes > 0 ? hs.bvh_max_depth + 2 : 0;
-    s->smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
-    e = (cudaError_t)(d.n_meshes > 0 ? occupancy_render_mesh(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, 0));
+    // parked per-lane state (render_kernel.cuh PK_SLOTS doubles per thread) + the BVH traversal stacks
+    s->smem = (size_t)RTC_PARK_SLOTS * RTC_BLOCK_THREADS * sizeof(double) +
+              (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
+    e = (cudaError_t)(d.n_meshes > 0 ? occupancy_render_mesh(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, s->smem));
     if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;
@@ -204,7 +206,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
     CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_render_mesh(s->d, P, s->grid, s->smem, stream)
-                                             : launch_render_analytic(s->d, P, s->grid, 0, stream)));
+                                             : launch_render_analytic(s->d, P, s->grid, s->smem, stream)));
     CUDA_TRY(cudaEventRecord(s->ev1, stream));
     unsigned long long c[8];
     CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, stream));
