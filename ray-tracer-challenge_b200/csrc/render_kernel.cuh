@@ -68,11 +68,17 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 
 // MESH: the scene has triangle meshes (BVH traversal compiled in; the traversal stacks follow the
 // parked state in dynamic shared memory).  Scenes without meshes run the instantiation without it.
-#ifndef RTC_MIN_BLOCKS
-#define RTC_MIN_BLOCKS 6  // 80 registers: measured best on B200 (latency-bound kernel: occupancy beats spills)
+// Resident CTAs per SM the register allocation aims for, measured on B200 (the kernel is latency-bound:
+// occupancy against spills).  Analytic scenes: 6 (80 registers); mesh scenes keep the traversal state of
+// mesh_inner / mesh_leaf in registers: 4 (128 registers).
+#ifndef RTC_MIN_BLOCKS_ANALYTIC
+#define RTC_MIN_BLOCKS_ANALYTIC 6
+#endif
+#ifndef RTC_MIN_BLOCKS_MESH
+#define RTC_MIN_BLOCKS_MESH 4
 #endif
 template <bool MESH>
-__global__ void __launch_bounds__(RTC_BLOCK, RTC_MIN_BLOCKS) render_kernel(DScene S, RenderParams P) {
+__global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
     double* pk = s_mem + threadIdx.x;
     int* stack = reinterpret_cast<int*>(s_mem + PK_SLOTS * RTC_BLOCK) + threadIdx.x;
