@@ -234,7 +234,7 @@ def main():
         return st
 
     def frame_on_rank0():
-        return peer.frame if peer is not None else gather.frame
+        return peer.frame if peer is not None else (gather.frame if world > 1 else gather.local)
 
     # the caller-owned canvas of the e2e leg: page-locked (rtc_host_alloc, what the Zig shim uses), so the kernel
     # stores pixels straight into host memory; a pageable canvas (staging frame + cudaMemcpy) is timed beside it

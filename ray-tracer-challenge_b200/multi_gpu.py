@@ -41,11 +41,12 @@ class GatherFrame:
 
     def assemble(self):
         """Call on every rank after rendering into `local`.  Returns the frame on rank 0, None elsewhere."""
-        if self.world > 1:
-            dist.gather(self.local, self.parts, dst=0)
+        if self.world == 1:
+            return self.local[: len(self.rows[0])]  # one partition holding every row in order: already the frame
+        dist.gather(self.local, self.parts, dst=0)
         if self.rank != 0:
             return None
-        src = self.parts if self.world > 1 else [self.local]
+        src = self.parts
         for r in range(self.world):
             n = len(self.rows[r])
             if n:
