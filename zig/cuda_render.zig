@@ -360,10 +360,13 @@ pub fn render(camera: Camera(T), allocator: Allocator, world: World(T)) !Canvas(
         for (0..4) |col| cam.inverse[r * 4 + col] = camera._inverse_transform.data[r][col];
     }
 
-    const rgb = try allocator.alloc(f64, camera.hsize * camera.vsize * 3);
-    defer allocator.free(rgb);
+    // page-locked staging canvas: the kernel stores finished pixels straight into it over PCIe
+    const n = camera.hsize * camera.vsize * 3;
+    const raw = c.rtc_host_alloc(n * @sizeOf(f64)) orelse return error.OutOfMemory;
+    defer c.rtc_host_free(raw);
+    const rgb: [*]f64 = @ptrCast(@alignCast(raw));
     var stats: c.rtc_stats = undefined;
-    if (c.rtc_render(scene, &cam, 5, null, rgb.ptr, &stats) != 0) return error.CudaRenderFailed;
+    if (c.rtc_render(scene, &cam, 5, null, rgb, &stats) != 0) return error.CudaRenderFailed;
     // Color(f64) is a packed struct (color.zig:9-15): copy, never alias.
     for (image.pixels, 0..) |*p, i| p.* = Color(T).new(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
     return image;
