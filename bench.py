@@ -163,10 +163,27 @@ def run_reference(args, rank):
                  "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "note": "C++ restatement of the reference CPU algorithm (oracle/); the Zig reference cannot be built "
                          "on this box; ms_per_step is the time of the SAMPLE, not of a full frame"})
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+def emit(line):
+    """The ONE JSON line of the contract goes to the process's real stdout; everything else that libraries write
+    to fd 1 (NCCL prints its version banner there) has been sent to stderr by quiet_stdout()."""
+    os.write(REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+REAL_STDOUT = 1
+
+
+def quiet_stdout():
+    global REAL_STDOUT
+    sys.stdout.flush()
+    REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -344,7 +361,7 @@ def main():
             r, s, desc = cpu_sample(threads)
             line["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
                                     "sample": desc}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
