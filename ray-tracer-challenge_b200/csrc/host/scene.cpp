@@ -1,6 +1,7 @@
 // Build-time operations on the host scene model (see scene.hpp for the reference map).
 #include "scene.hpp"
 
+#include <cstring>
 #include <atomic>
 
 namespace rtc {
@@ -101,10 +102,22 @@ void Shape::set_transform(const Mat4& m) {
             left->set_transform(m.mul(left->transform));
             right->set_transform(m.mul(right->transform));
             break;
-        default:
+        default: {
             transform = m;
-            inverse = m.inverse();
-            inverse_transpose = inverse.transpose();
+            psb_valid = false;
+            // The triangles of a mesh all receive the same matrix: same input, same inverse (matrix.zig:202-217
+            // is deterministic), so the last result is reused instead of 140,940 x nesting-depth inversions.
+            static thread_local Mat4 last_m, last_inv, last_inv_t;
+            static thread_local bool have_last = false;
+            if (!have_last || std::memcmp(&last_m, &m, sizeof(Mat4)) != 0) {
+                last_inv = m.inverse();
+                last_inv_t = last_inv.transpose();
+                last_m = m;
+                have_last = true;
+            }
+            inverse = last_inv;
+            inverse_transpose = last_inv_t;
+        }
     }
 }
 
@@ -154,6 +167,9 @@ void Shape::partition_children(std::vector<Shape>& left, std::vector<Shape>& rig
     BBox lb, rb;
     bbox.split(lb, rb);
     std::vector<Shape> keep;
+    left.reserve(children.size());
+    right.reserve(children.size());
+    keep.reserve(children.size());
     for (Shape& c : children) {
         BBox cb = c.parent_space_bounds();
         if (lb.contains_box(cb))
@@ -168,6 +184,7 @@ void Shape::partition_children(std::vector<Shape>& left, std::vector<Shape>& rig
 
 void Shape::make_subgroup(std::vector<Shape>& members) {
     Shape sub = Shape::group();
+    sub.children.reserve(members.size());
     for (Shape& m : members) sub.add_child(std::move(m));
     add_child(std::move(sub));
 }

@@ -145,6 +145,9 @@ struct Shape {
     CsgOp op = CsgOp::Union;
     // group + csg : `_bbox`
     BBox bbox;
+    // cache of parent_space_bounds() for triangles
+    mutable BBox psb;
+    mutable bool psb_valid = false;
 
     static size_t next_id();
     static Shape make(ShapeKind k) {
@@ -174,7 +177,16 @@ struct Shape {
     bool is_leaf() const { return kind != ShapeKind::Group && kind != ShapeKind::Csg; }
     void set_transform(const Mat4& m);       // shape.zig:286-310 (groups/CSG push down)
     BBox bounds() const;                     // object-space bounds per variant
-    BBox parent_space_bounds() const { return bounds().transform(transform); }
+    // shape.zig:364-370.  For triangles (the only kind a scene holds by the hundred thousand, and whose
+    // bounds are asked for again at every level of divide()) the result is kept; set_transform resets it.
+    BBox parent_space_bounds() const {
+        if (kind != ShapeKind::Triangle && kind != ShapeKind::SmoothTriangle) return bounds().transform(transform);
+        if (!psb_valid) {
+            psb = bounds().transform(transform);
+            psb_valid = true;
+        }
+        return psb;
+    }
     void add_child(Shape child);             // group.zig:75-78
     void divide(size_t threshold);           // shape.zig:372-399
     void partition_children(std::vector<Shape>& left, std::vector<Shape>& right);  // group.zig:85-115
