@@ -23,7 +23,7 @@ $(OBJDIR)/%.o: $(CSRC)/% $(HDR) Makefile
 	@mkdir -p $(dir $@)
 	$(NVCC) $(NVFLAGS) -c -o $@ $<
 $(OUT): $(OBJ)
-	$(NVCC) $(NVFLAGS) -shared -o $@ $(OBJ) -lz
+	$(NVCC) $(NVFLAGS) -shared -o $@ $(OBJ) -lz -lpthread
 
 oracle:
 	$(MAKE) -C oracle all

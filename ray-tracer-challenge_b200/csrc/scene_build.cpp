@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstring>
 #include <map>
+#include <future>
 #include <stdexcept>
 
 #include "bvh.hpp"
@@ -255,8 +256,16 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         }
     }
     hs.bvh_max_depth = 0;
+    // the meshes are independent: one builder thread each (dragons.json: 6 x 23,490 triangles)
+    std::vector<std::future<BvhBuild>> builds;
     for (auto& kv : groups) {
-        BvhBuild b = build_bvh(kv.second);
+        const std::vector<DTri>* tris = &kv.second;
+        builds.push_back(std::async(groups.size() > 1 ? std::launch::async : std::launch::deferred,
+                                    [tris] { return build_bvh(*tris); }));
+    }
+    size_t build_i = 0;
+    for (auto& kv : groups) {
+        BvhBuild b = builds[build_i++].get();
         DMesh m{};
         m.transform = kv.first.first;
         m.flags = kv.first.second;
