@@ -115,6 +115,38 @@ def test_render_device_frame_partitions(pkg):
     assert 0 < full.stats.shadow_rays_culled < full.stats.shadow_rays
 
 
+@pytest.mark.parametrize("w,h", [(1, 1), (13, 7), (8, 4), (9, 5), (257, 3)])
+def test_ragged_frame_sizes(pkg, oracle, w, h):
+    """Frames that are not a multiple of the 8x4 work tiles (and the 1x1 frame) against the oracle."""
+    compare(pkg, oracle, scenes.SMOKE_SCENE, "", w, h, min_frac=0.99 if w * h > 100 else 1.0, label="ragged")
+
+
+@pytest.mark.parametrize("depth", [0, 1, 7])
+def test_recursion_depths(pkg, oracle, depth):
+    """remaining_recursions other than the shipped 5 (camera.zig:118), incl. 0 (no secondary rays at all)."""
+    info = pkg.parse_scene(scenes.SMOKE_SCENE, "", 64, 48)
+    got = info.camera.render(info.world, max_depth=depth)
+    ref = oracle.OracleScene(json_text=scenes.SMOKE_SCENE, width=64, height=48)
+    want, counts = ref.render(max_depth=depth)
+    assert (np.abs(got.pixels - want).max(axis=2) <= TOL).mean() >= 0.999
+    assert got.stats.secondary_rays == counts["secondary"]
+    if depth == 0:
+        assert got.stats.secondary_rays == 0
+
+
+def test_empty_world_and_no_lights(pkg, oracle):
+    import json
+    base = json.loads(scenes.default_world(16, 12))
+    empty = dict(base, objects=[])
+    info = pkg.parse_scene(json.dumps(empty), "")
+    img = info.camera.render(info.world)
+    assert not img.pixels.any() and img.stats.primary_rays == 16 * 12 and img.stats.shadow_rays == 0
+    dark = dict(base, lights=[])
+    info = pkg.parse_scene(json.dumps(dark), "")
+    img = info.camera.render(info.world)  # shadeHit sums over zero lights: black, no shadow rays (world.zig:89-96)
+    assert not img.pixels.any() and img.stats.shadow_rays == 0
+
+
 def test_errors(pkg):
     with pytest.raises(pkg.RtcError):
         pkg.World(b"\0" * 512)
