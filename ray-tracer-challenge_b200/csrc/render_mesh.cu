@@ -1,5 +1,6 @@
 // Instantiation of the render kernel for scenes WITH triangle meshes (see render_kernel.cuh).
 #include "render_kernel.cuh"
+#include "render_wavefront.cuh"
 
 namespace rtc {
 
@@ -12,6 +13,17 @@ int occupancy_render_mesh(int* blocks_per_sm, size_t smem) {
     cudaError_t e = cudaFuncSetAttribute(render_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel<true>, RTC_BLOCK, smem);
+}
+
+int launch_wave_mesh(const DScene& S, const WaveParams& W, int grid, size_t smem, cudaStream_t stream) {
+    wave_kernel<true><<<grid, RTC_BLOCK, smem, stream>>>(S, W);
+    return (int)cudaGetLastError();
+}
+
+int occupancy_wave_mesh(int* blocks_per_sm, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(wave_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, wave_kernel<true>, RTC_BLOCK, smem);
 }
 
 }  // namespace rtc

@@ -31,6 +31,71 @@ struct RenderParams {
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };
 
+// ---- wavefront path (render_wavefront.cuh) ------------------------------------------------------------
+// One ray of recursion level d waiting for its closest-hit query (colorAt, world.zig:111-123).  64 bytes.
+struct WRay {
+    double ox, oy, oz, dx, dy, dz;
+    double w;  // product of the reflective / transparency / Schlick factors on the path from the eye
+    int remaining;  // remaining_recursions (world.zig:160, :178)
+    int pix;        // pixel of the partition (packed row-major index)
+};
+static_assert(sizeof(WRay) == 64, "WRay must be 64 bytes");
+// One shaded hit waiting for its shadow queries: everything lighting() needs (material.zig:40-74).  128 bytes.
+struct WHit {
+    double over[3];    // over_point
+    double normal[3];  // normalv (flipped towards the eye)
+    double rd[3];      // ray direction (eyev = -rd)
+    double color[3];   // pattern colour at over_point
+    double w;
+    int mat, pix;
+    double pad[2];
+};
+static_assert(sizeof(WHit) == 128, "WHit must be 128 bytes");
+
+#define RTC_WF_LEVELS 9  // recursion levels 0..max_depth (<= 7) + 1
+// counters (u64), all zeroed before a frame
+enum {
+    WC_ERR = 0,        // error bits
+    WC_SHADOW = 1,     // shadow rays (incl. culled)
+    WC_CULLED = 2,
+    WC_NRAYS = 8,      // [level] rays queued for that level (level 0: unused, primaries are generated)
+    WC_NHITS = 24,     // [level] hit records of that level
+    WC_TAKE_RAY = 40,  // [level] consumer cursor over the rays of that level
+    WC_TAKE_SHADOW = 56,  // [level] consumer cursor over (hit record, light) pairs of that level
+    WC_COUNT = 72
+};
+
+struct WaveParams {
+    DCamera cam;
+    int max_depth, level;
+    unsigned int tile_rows, part, n_parts;
+    unsigned long long rows, n_pixels;  // of this partition
+    const WRay* rays_in;   // rays of `level` (level 0: NULL, generated from the camera)
+    WRay* rays_out;        // rays of level + 1
+    const WHit* hits_in;   // hits of level - 1: their shadow queries run in this launch
+    WHit* hits_out;        // hits of `level`
+    unsigned long long cap;  // capacity (entries) of each queue
+    long long* acc;          // fixed-point RGB accumulators, 3 per pixel of the partition
+    double scale;            // accumulator units per 1.0
+    unsigned long long* counters;
+};
+
+struct ResolveParams {
+    unsigned long long hsize, rows, n_pixels;
+    unsigned int tile_rows, part, n_parts;
+    int full_frame;
+    const long long* acc;
+    double inv_scale;
+    double* out;
+    unsigned char* out8;
+};
+
+int launch_wave_mesh(const DScene& S, const WaveParams& W, int grid, size_t smem, cudaStream_t stream);
+int launch_wave_analytic(const DScene& S, const WaveParams& W, int grid, size_t smem, cudaStream_t stream);
+int occupancy_wave_mesh(int* blocks_per_sm, size_t smem);
+int occupancy_wave_analytic(int* blocks_per_sm, size_t smem);
+int launch_resolve(const ResolveParams& R, cudaStream_t stream);
+
 // render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
 // smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).
 int launch_render_mesh(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream);

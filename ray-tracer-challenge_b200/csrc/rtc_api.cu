@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/rtc_b200.h: scene upload, render calls, host loader.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -38,8 +39,27 @@ struct rtc_scene {
     size_t d_frame_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int grid = 0;
-    size_t smem = 0;  // dynamic shared memory per CTA: the BVH traversal stacks
+    size_t smem = 0;  // dynamic shared memory per CTA: parked state + the BVH traversal stacks
+    // wavefront path (render_wavefront.cuh): per-level queues, fixed-point accumulators, counters
+    int wf_grid = 0;
+    size_t wf_smem = 0;
+    double wf_scale = 1.0;
+    unsigned long long wf_cap = 0;   // entries per queue
+    size_t wf_pixels = 0;            // pixels the accumulators hold
+    WRay* wf_rays[2] = {nullptr, nullptr};
+    WHit* wf_hits[2] = {nullptr, nullptr};
+    long long* wf_acc = nullptr;
+    unsigned long long* wf_counters = nullptr;
 };
+
+// RTC_KERNEL=mega selects the per-pixel megakernel (render_kernel.cuh); default is the wavefront path.
+static bool use_megakernel() {
+    static const bool v = [] {
+        const char* e = std::getenv("RTC_KERNEL");
+        return e && std::string(e) == "mega";
+    }();
+    return v;
+}
 
 extern "C" {
 
@@ -76,6 +96,12 @@ void rtc_scene_destroy(rtc_scene* s) {
     cudaSetDevice(s->device);
     if (s->slab) cudaFree(s->slab);
     if (s->d_counters) cudaFree(s->d_counters);
+    for (int i = 0; i < 2; i++) {
+        if (s->wf_rays[i]) cudaFree(s->wf_rays[i]);
+        if (s->wf_hits[i]) cudaFree(s->wf_hits[i]);
+    }
+    if (s->wf_acc) cudaFree(s->wf_acc);
+    if (s->wf_counters) cudaFree(s->wf_counters);
     if (s->d_frame) cudaFree(s->d_frame);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -169,7 +195,133 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;
+    // wavefront kernels: no parked state, only the traversal stacks
+    s->wf_smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
+    int wf_per_sm = 0;
+    e = (cudaError_t)(d.n_meshes > 0 ? occupancy_wave_mesh(&wf_per_sm, s->wf_smem) : occupancy_wave_analytic(&wf_per_sm, s->wf_smem));
+    if (e != cudaSuccess) return bail(e, "occupancy query (wavefront)");
+    if (wf_per_sm < 1) wf_per_sm = 1;
+    s->wf_grid = prop.multiProcessorCount * wf_per_sm;
+    // Fixed-point unit of the pixel accumulators: a pixel is a sum of at most 2^(depth+1) terms weight x lighting(),
+    // weight <= 1, |lighting()| <= sum over lights |I| x (ambient + diffuse + specular) x max |colour|.
+    {
+        double li = 0.0, coef = 1.0, col = 1.0;
+        for (const rtc_light& l : hs.lights)
+            li += std::fmax(std::fabs(l.intensity[0]), std::fmax(std::fabs(l.intensity[1]), std::fabs(l.intensity[2])));
+        for (const rtc_material& m : hs.materials)
+            coef = std::fmax(coef, std::fabs(m.ambient) + std::fabs(m.diffuse) + std::fabs(m.specular));
+        for (const rtc_pattern& pt : hs.patterns)
+            for (int k = 0; k < 3; k++) col = std::fmax(col, std::fabs(pt.color[k]));
+        double bound = 256.0 * std::fmax(li, 1.0) * coef * col;
+        int ex = 0;
+        if (!(bound < 1e300)) bound = 1e300;
+        std::frexp(bound, &ex);          // bound < 2^ex
+        int sh = 62 - ex;
+        if (sh > 52) sh = 52;            // never finer than a double's own resolution at 1.0
+        if (sh < -900) sh = -900;
+        s->wf_scale = std::ldexp(1.0, sh);
+    }
     *out = s;
+    return RTC_OK;
+}
+
+// Grows (never shrinks) the wavefront buffers of a scene for a partition of n_pixels pixels.
+static int ensure_wavefront(rtc_scene* s, size_t n_pixels) {
+    if (!s->wf_counters) CUDA_TRY(cudaMalloc(&s->wf_counters, WC_COUNT * sizeof(unsigned long long)));
+    if (s->wf_pixels >= n_pixels) return RTC_OK;
+    for (int i = 0; i < 2; i++) {
+        if (s->wf_rays[i]) cudaFree(s->wf_rays[i]);
+        if (s->wf_hits[i]) cudaFree(s->wf_hits[i]);
+        s->wf_rays[i] = nullptr;
+        s->wf_hits[i] = nullptr;
+    }
+    if (s->wf_acc) cudaFree(s->wf_acc);
+    s->wf_acc = nullptr;
+    s->wf_pixels = 0;
+    // a level holds at most min(2^d, ...) x pixels rays; 3 x pixels covers every shipped scene with room to
+    // spare, and a frame that overflows is redone by the megakernel (never truncated)
+    unsigned long long cap = 3ull * n_pixels + (1ull << 16);
+    for (int i = 0; i < 2; i++) {
+        CUDA_TRY(cudaMalloc(&s->wf_rays[i], cap * sizeof(WRay)));
+        CUDA_TRY(cudaMalloc(&s->wf_hits[i], cap * sizeof(WHit)));
+    }
+    CUDA_TRY(cudaMalloc(&s->wf_acc, n_pixels * 3 * sizeof(long long)));
+    s->wf_cap = cap;
+    s->wf_pixels = n_pixels;
+    return RTC_OK;
+}
+
+// The frame as max_depth + 2 wavefront launches + one resolve (render_wavefront.cuh).
+static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t stream, rtc_stats* stats) {
+    const size_t n_pixels = (size_t)(P.rows * P.cam.hsize);
+    if (n_pixels >= (1ull << 31)) return fail(RTC_ERR_INVALID, "render: partition larger than 2^31 pixels");
+    int rc = ensure_wavefront(s, n_pixels);
+    if (rc) return rc;
+    WaveParams W{};
+    W.cam = P.cam;
+    W.max_depth = P.max_depth;
+    W.tile_rows = P.tile_rows;
+    W.part = P.part;
+    W.n_parts = P.n_parts;
+    W.rows = P.rows;
+    W.n_pixels = n_pixels;
+    W.cap = s->wf_cap;
+    W.acc = s->wf_acc;
+    W.scale = s->wf_scale;
+    W.counters = s->wf_counters;
+    CUDA_TRY(cudaMemsetAsync(s->wf_counters, 0, WC_COUNT * sizeof(unsigned long long), stream));
+    CUDA_TRY(cudaEventRecord(s->ev0, stream));
+    CUDA_TRY(cudaMemsetAsync(s->wf_acc, 0, n_pixels * 3 * sizeof(long long), stream));
+    const int n_launch = P.max_depth + 2;
+    for (int level = 0; level < n_launch; level++) {
+        W.level = level;
+        W.rays_in = s->wf_rays[level & 1];
+        W.rays_out = s->wf_rays[(level + 1) & 1];
+        W.hits_in = s->wf_hits[(level + 1) & 1];
+        W.hits_out = s->wf_hits[level & 1];
+        CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_wave_mesh(s->d, W, s->wf_grid, s->wf_smem, stream)
+                                                 : launch_wave_analytic(s->d, W, s->wf_grid, s->wf_smem, stream)));
+    }
+    ResolveParams R{};
+    R.hsize = P.cam.hsize;
+    R.rows = P.rows;
+    R.n_pixels = n_pixels;
+    R.tile_rows = P.tile_rows;
+    R.part = P.part;
+    R.n_parts = P.n_parts;
+    R.full_frame = P.full_frame;
+    R.acc = s->wf_acc;
+    R.inv_scale = 1.0 / s->wf_scale;
+    R.out = P.out;
+    R.out8 = P.out8;
+    CUDA_TRY((cudaError_t)launch_resolve(R, stream));
+    CUDA_TRY(cudaEventRecord(s->ev1, stream));
+    unsigned long long c[WC_COUNT];
+    CUDA_TRY(cudaMemcpyAsync(c, s->wf_counters, sizeof c, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    if (c[WC_ERR] & 16ull) return RTC_ERR_CAPACITY + 1000;  // ERR_QUEUE: the caller redoes the frame with the megakernel
+    if (stats) {
+        unsigned long long hits = 0, secondary = 0;
+        for (int l = 0; l <= P.max_depth; l++) hits += c[WC_NHITS + l];
+        for (int l = 1; l <= P.max_depth; l++) secondary += c[WC_NRAYS + l];
+        stats->primary_rays = n_pixels;
+        stats->shadow_rays = hits * (unsigned long long)s->d.n_lights;
+        stats->secondary_rays = secondary;
+        stats->pixels = n_pixels;
+        stats->kernel_ms = ms;
+        stats->launches = (unsigned long long)n_launch + 1;
+        stats->shadow_rays_culled = c[WC_CULLED];
+    }
+    if (c[WC_ERR]) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf,
+                      "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
+                      "4=CSG list, 8=BVH stack)",
+                      c[WC_ERR]);
+        return fail(RTC_ERR_CAPACITY, buf);
+    }
     return RTC_OK;
 }
 
@@ -203,6 +355,10 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.counters = s->d_counters;
     if (stats) std::memset(stats, 0, sizeof *stats);
     if (P.rows == 0) return RTC_OK;
+    if (!use_megakernel()) {
+        int rc = render_wavefront(s, P, stream, stats);
+        if (rc != RTC_ERR_CAPACITY + 1000) return rc;  // queue overflow: redo the frame with the megakernel below
+    }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
     CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_render_mesh(s->d, P, s->grid, s->smem, stream)
