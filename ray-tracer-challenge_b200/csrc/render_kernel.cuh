@@ -45,10 +45,10 @@ __device__ __forceinline__ unsigned char quantise(double c) {
 enum {
     PK_RO = 0,       // current ray origin
     PK_RD = 3,       // current ray direction
-    PK_PCOL = 6,     // colour accumulated for the current pixel
+    PK_PCOL = 6,     // colour accumulated for the current pixel: three int64 in fixed point (bit-cast into the slots)
     PK_NORMAL = 9,   // hit normal (flipped towards the eye)
     PK_COLOR = 12,   // pattern colour at the hit
-    PK_SURFACE = 15, // sum of lighting() over the lights so far
+    PK_SPARE = 15,   // (three free slots)
     PK_RW = 18,      // product of the reflective / transparency / Schlick factors along the path
     PK_N1 = 19,
     PK_N2 = 20,
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         PK(PK_RW) = 1.0;
                         remaining = P.max_depth;
                         pix = (long long)((P.full_frame ? y : pr) * P.cam.hsize + px);
-                        pk_st(pk, PK_PCOL, v3(0, 0, 0));
+                        pk_st(pk, PK_PCOL, v3(0, 0, 0));  // +0.0 is also the bit pattern of int64 0
                         rsp = 0;
                         state = ST_CLOSEST;
                         n_primary++;
@@ -244,7 +244,6 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
                 pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
-                pk_st(pk, PK_SURFACE, v3(0, 0, 0));
                 h_light = 0;
                 PK(PK_N1) = 1.0;
                 PK(PK_N2) = 1.0;
@@ -286,7 +285,20 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     sum = sum + diffuse + spec;
                 }
             }
-            pk_st(pk, PK_SURFACE, pk_ld(pk, PK_SURFACE) + sum);
+            // shadeHit is linear: weight x lighting() of THIS light goes straight into the pixel, as an exact
+            // integer addition (fixed point, P.scale units per 1.0).  Exact means order-independent: the frame is
+            // bit-identical whatever the partition, the lane assignment or the kernel (the wavefront path adds
+            // the very same terms, render_wavefront.cuh wf_add).
+            {
+                V3 c = sum * PK(PK_RW);
+                double v[3] = {c.x * P.scale, c.y * P.scale, c.z * P.scale};
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    if (!(fabs(v[k]) < 9.0e18)) continue;
+                    long long a = __double_as_longlong(PK(PK_PCOL + k)) + __double2ll_rn(v[k]);
+                    PK(PK_PCOL + k) = __longlong_as_double(a);
+                }
+            }
             h_light++;
             if (h_light >= S.n_lights) state = -1;
         }
@@ -296,7 +308,6 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
             const rtc_material& M = S.materials[h_mat];
             const double rw = PK(PK_RW), h_n1 = PK(PK_N1), h_n2 = PK(PK_N2);
             const V3 ro = pk_ld(pk, PK_RO), rd = pk_ld(pk, PK_RD), h_normal = pk_ld(pk, PK_NORMAL);
-            pk_st(pk, PK_PCOL, pk_ld(pk, PK_PCOL) + pk_ld(pk, PK_SURFACE) * rw);
             V3 eyev = neg(rd);
             double refl_w = 0.0, refr_w = 0.0;
             V3 refr_dir = v3(0, 0, 0);
@@ -362,7 +373,10 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 remaining = tk.remaining;
                 state = ST_CLOSEST;
             } else {
-                V3 pcol = pk_ld(pk, PK_PCOL);
+                const double inv_scale = 1.0 / P.scale;  // a power of two: exact
+                V3 pcol = v3((double)__double_as_longlong(PK(PK_PCOL)) * inv_scale,
+                             (double)__double_as_longlong(PK(PK_PCOL + 1)) * inv_scale,
+                             (double)__double_as_longlong(PK(PK_PCOL + 2)) * inv_scale);
                 if (P.out8) {
                     uchar4 c = make_uchar4(quantise(pcol.x), quantise(pcol.y), quantise(pcol.z), 255);
                     reinterpret_cast<uchar4*>(P.out8)[pix] = c;

@@ -25,6 +25,7 @@ struct RenderParams {
     unsigned long long rows;       // rows of this partition
     unsigned long long n_items;    // tiles_x * tiles_y * 32 work items (some fall outside the frame)
     unsigned int tiles_x;
+    double scale;                  // fixed-point units per 1.0 of the pixel accumulators (a power of two)
     int full_frame;                // 0: out holds the packed rows of the partition; 1: the whole frame
     double* out;                   // 3 doubles per pixel (may be peer-mapped memory of another GPU)
     unsigned char* out8;           // or RGBA8 (NULL when `out` is used)
@@ -68,6 +69,8 @@ enum {
 struct WaveParams {
     DCamera cam;
     int max_depth, level;
+    int inline_shadows;  // rays of this level trace the shadow rays of their own hit (no hit records)
+    int shadow_stage;    // this launch runs the shadow queries of the previous level's hit records
     unsigned int tile_rows, part, n_parts;
     unsigned long long rows, n_pixels;  // of this partition
     const WRay* rays_in;   // rays of `level` (level 0: NULL, generated from the camera)

@@ -83,6 +83,48 @@ __device__ __forceinline__ void wf_store_ray(WRay* dst, V3 o, V3 d, double w, in
     p[3] = make_double2(w, __hiloint2double(pix, remaining));
 }
 
+// lighting() of one (hit, light) pair, shadow query included: World.isShadowed (world.zig:126-135) +
+// Material.lighting (material.zig:40-74).  Warp-wide call (live = this lane has a pair).
+template <bool MESH>
+__device__ __forceinline__ V3 wf_light(const DScene& S, V3 over, V3 normal, V3 rd, V3 color, int mat, int li, bool live,
+                                       int* stack, int* err, unsigned& n_culled) {
+    const rtc_light& Lg = S.lights[li];
+    V3 dir = v3(Lg.position[0], Lg.position[1], Lg.position[2]) - over;
+    double dist = sqrt(dot(dir, dir));
+    Query q;
+    q.mode = Q_SHADOW;
+    q.o = over;
+    q.d = v3(dir.x / dist, dir.y / dist, dir.z / dist);
+    q.t = dist;
+    q.leaf = -1;
+    q.a = q.b = 0.0;
+    q.c_leaf = -1;
+    q.flag = 0;
+    // Light behind the surface: lighting() yields ambient whether or not the point is shadowed
+    // (material.zig:55-63), so the ray need not be traced.  Counted as a shadow ray, reported as culled.
+    const double ldn = dot(q.d, normal);
+    const bool trace_it = live && (ldn >= 0.0);
+    if (live && !trace_it) n_culled++;
+    wf_trace<MESH>(q, S, stack, err, trace_it);
+    V3 sum = v3(0, 0, 0);
+    if (live) {
+        const rtc_material& M = S.materials[mat];
+        V3 li3 = v3(Lg.intensity[0], Lg.intensity[1], Lg.intensity[2]);
+        V3 eff = v3(color.x * li3.x, color.y * li3.y, color.z * li3.z);
+        sum = eff * M.ambient;
+        if (trace_it && !q.flag) {
+            V3 lightv = q.d;
+            V3 diffuse = eff * (M.diffuse * ldn);
+            V3 reflectv = lightv - normal * (2.0 * dot(lightv, normal));  // tuple.zig reflect
+            double rde = dot(neg(reflectv), neg(rd));
+            V3 spec = v3(0, 0, 0);
+            if (rde > 0.0) spec = li3 * (M.specular * zig_pow(rde, M.shininess));
+            sum = sum + diffuse + spec;
+        }
+    }
+    return sum;
+}
+
 template <bool MESH>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_WF_BLOCKS_MESH : RTC_WF_BLOCKS_ANALYTIC)
 wave_kernel(DScene S, WaveParams W) {
@@ -224,7 +266,29 @@ wave_kernel(DScene S, WaveParams W) {
                 }
             }
             // ---- hit record for the shadow queries of the next launch (shadeHit, world.zig:89-96) ---
-            if (S.n_lights > 0) {
+            if (W.inline_shadows) {
+                // the lane traces the shadow rays of its own hit, light after light (all lanes of the warp are at
+                // the same light at the same time), and adds weight x surface once.  Level 0 STORES: every pixel
+                // has exactly one primary ray, so this also initialises the accumulators (no memset, no atomics).
+                V3 over = point + normal * 1e-5;
+                V3 surface = v3(0, 0, 0);
+#pragma unroll 1
+                for (int li = 0; li < S.n_lights; li++)
+                    surface = surface + wf_light<MESH>(S, over, normal, q.d, color, mat, li, hit, stack, &err, n_culled);
+                unsigned hm = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0 && hm) atomicAdd(C + WC_NHITS + level, (unsigned long long)__popc(hm));
+                if (live) {
+                    if (level == 0) {
+                        V3 c = surface * rw;
+                        double v[3] = {c.x * W.scale, c.y * W.scale, c.z * W.scale};
+#pragma unroll
+                        for (int k = 0; k < 3; k++)
+                            W.acc[3ll * pix + k] = (hit && fabs(v[k]) < 9.0e18) ? __double2ll_rn(v[k]) : 0ll;
+                    } else if (hit) {
+                        wf_add(W.acc, pix, surface * rw, W.scale);
+                    }
+                }
+            } else if (S.n_lights > 0) {
                 unsigned long long slot = wf_reserve(hit, C + WC_NHITS + level, W.cap, lane, lt_mask, &err);
                 if (slot != ~0ull) {
                     V3 over = point + normal * 1e-5;
@@ -288,7 +352,7 @@ wave_kernel(DScene S, WaveParams W) {
     }
 
     // ================= shadow queries of the previous level's hits: isShadowed + lighting ================
-    if (level > 0 && S.n_lights > 0) {
+    if (W.shadow_stage && level > 0 && S.n_lights > 0) {
         const unsigned long long L = (unsigned long long)S.n_lights;
         unsigned long long n_hits = C[WC_NHITS + level - 1] < W.cap ? C[WC_NHITS + level - 1] : W.cap;
         const unsigned long long n_tasks = n_hits * L;
@@ -298,50 +362,14 @@ wave_kernel(DScene S, WaveParams W) {
             base = __shfl_sync(0xffffffffu, base, 0);
             if (base >= n_tasks) break;
             const unsigned long long task = base + lane;
-            bool live = task < n_tasks;
+            const bool live = task < n_tasks;
             const unsigned long long rec = live ? task / L : 0;
             const int li = live ? (int)(task % L) : 0;
             const double2* p = reinterpret_cast<const double2*>(W.hits_in + rec);
             double2 a = p[0], b = p[1], c = p[2], e = p[3], f = p[4], g = p[5], h = p[6];
             const V3 over = v3(a.x, a.y, b.x), normal = v3(b.y, c.x, c.y), rd = v3(e.x, e.y, f.x), color = v3(f.y, g.x, g.y);
-            const double rw = h.x;
-            const int mat = __double2loint(h.y), pix = __double2hiint(h.y);
-            const rtc_light& Lg = S.lights[li];
-            // World.isShadowed (world.zig:126-135)
-            V3 dir = v3(Lg.position[0], Lg.position[1], Lg.position[2]) - over;
-            double dist = sqrt(dot(dir, dir));
-            Query q;
-            q.mode = Q_SHADOW;
-            q.o = over;
-            q.d = v3(dir.x / dist, dir.y / dist, dir.z / dist);
-            q.t = dist;
-            q.leaf = -1;
-            q.a = q.b = 0.0;
-            q.c_leaf = -1;
-            q.flag = 0;
-            // Light behind the surface: lighting() yields ambient whether or not the point is shadowed
-            // (material.zig:55-63), so the ray need not be traced.  Counted as a shadow ray, reported as culled.
-            const double ldn = dot(q.d, normal);
-            bool trace_it = live && (ldn >= 0.0);
-            if (live && !trace_it) n_culled++;
-            wf_trace<MESH>(q, S, stack, &err, trace_it);
-            if (live) {
-                // Material.lighting (material.zig:40-74)
-                const rtc_material& M = S.materials[mat];
-                V3 li3 = v3(Lg.intensity[0], Lg.intensity[1], Lg.intensity[2]);
-                V3 eff = v3(color.x * li3.x, color.y * li3.y, color.z * li3.z);
-                V3 sum = eff * M.ambient;
-                if (trace_it && !q.flag) {
-                    V3 lightv = q.d;
-                    V3 diffuse = eff * (M.diffuse * ldn);
-                    V3 reflectv = lightv - normal * (2.0 * dot(lightv, normal));  // tuple.zig reflect
-                    double rde = dot(neg(reflectv), neg(rd));
-                    V3 spec = v3(0, 0, 0);
-                    if (rde > 0.0) spec = li3 * (M.specular * zig_pow(rde, M.shininess));
-                    sum = sum + diffuse + spec;
-                }
-                wf_add(W.acc, pix, sum * rw, W.scale);
-            }
+            V3 sum = wf_light<MESH>(S, over, normal, rd, color, __double2loint(h.y), li, live, stack, &err, n_culled);
+            if (live) wf_add(W.acc, __double2hiint(h.y), sum * h.x, W.scale);
         }
     }
 

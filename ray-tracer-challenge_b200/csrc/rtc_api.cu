@@ -50,15 +50,22 @@ struct rtc_scene {
     WHit* wf_hits[2] = {nullptr, nullptr};
     long long* wf_acc = nullptr;
     unsigned long long* wf_counters = nullptr;
+    bool has_secondary = false;  // some material is reflective or transparent: rays beyond level 0 can exist
+    // Which of the two kernels renders this scene faster is MEASURED (the answer depends on the scene: the
+    // wavefront wins where pixels have long or branching ray trees, the megakernel where they do not and on
+    // small frames): frames 1-4 alternate between the heuristic choice and the other kernel, later frames use the faster one.
+    int frames = 0;
+    float best_ms[2] = {-1.0f, -1.0f};  // [0] megakernel, [1] wavefront; per pixel-count of the last frame
+    size_t tuned_pixels = 0;
 };
 
-// RTC_KERNEL=mega selects the per-pixel megakernel (render_kernel.cuh); default is the wavefront path.
-static bool use_megakernel() {
-    static const bool v = [] {
-        const char* e = std::getenv("RTC_KERNEL");
-        return e && std::string(e) == "mega";
-    }();
-    return v;
+// RTC_KERNEL=mega|wave pins the kernel; default (auto) measures both on the first four frames of a scene.
+static int forced_kernel() {  // read at every render: tests switch it between frames
+    const char* e = std::getenv("RTC_KERNEL");
+    if (!e) return -1;
+    if (std::string(e) == "mega") return 0;
+    if (std::string(e) == "wave") return 1;
+    return -1;
 }
 
 extern "C" {
@@ -197,6 +204,8 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     s->grid = prop.multiProcessorCount * per_sm;
     // wavefront kernels: no parked state, only the traversal stacks
     s->wf_smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
+    for (const rtc_material& m : hs.materials)
+        if (m.reflective != 0.0 || m.transparency != 0.0) s->has_secondary = true;
     int wf_per_sm = 0;
     e = (cudaError_t)(d.n_meshes > 0 ? occupancy_wave_mesh(&wf_per_sm, s->wf_smem) : occupancy_wave_analytic(&wf_per_sm, s->wf_smem));
     if (e != cudaSuccess) return bail(e, "occupancy query (wavefront)");
@@ -223,6 +232,16 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     }
     *out = s;
     return RTC_OK;
+}
+
+// RTC_WF_INLINE: recursion levels whose shadow rays are traced inline by the lane that found the hit (default 0:
+// measured slower than separate shadow tasks on every config but skybox 4K; kept as a knob).
+static int wf_inline_levels() {
+    static const int v = [] {
+        const char* e = std::getenv("RTC_WF_INLINE");
+        return e ? std::atoi(e) : 0;
+    }();
+    return v;
 }
 
 // Grows (never shrinks) the wavefront buffers of a scene for a partition of n_pixels pixels.
@@ -271,10 +290,17 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
     W.counters = s->wf_counters;
     CUDA_TRY(cudaMemsetAsync(s->wf_counters, 0, WC_COUNT * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
-    CUDA_TRY(cudaMemsetAsync(s->wf_acc, 0, n_pixels * 3 * sizeof(long long), stream));
-    const int n_launch = P.max_depth + 2;
+    // levels below wf_inline_levels() trace the shadow rays of a hit in the lane that found it; level 0 then
+    // initialises the accumulators itself
+    const int inl = wf_inline_levels();
+    if (inl < 1) CUDA_TRY(cudaMemsetAsync(s->wf_acc, 0, n_pixels * 3 * sizeof(long long), stream));
+    // without reflective / transparent materials no ray beyond level 0 can exist: level 0 + its shadows
+    const int depth = s->has_secondary ? P.max_depth : 0;
+    const int n_launch = depth + ((depth < inl) ? 1 : 2);
     for (int level = 0; level < n_launch; level++) {
         W.level = level;
+        W.inline_shadows = level < inl;
+        W.shadow_stage = level > 0 && (level - 1) >= inl;
         W.rays_in = s->wf_rays[level & 1];
         W.rays_out = s->wf_rays[(level + 1) & 1];
         W.hits_in = s->wf_hits[(level + 1) & 1];
@@ -311,7 +337,7 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
         stats->secondary_rays = secondary;
         stats->pixels = n_pixels;
         stats->kernel_ms = ms;
-        stats->launches = (unsigned long long)n_launch + 1;
+        stats->launches = (unsigned long long)n_launch + 1;  // + resolve
         stats->shadow_rays_culled = c[WC_CULLED];
     }
     if (c[WC_ERR]) {
@@ -350,14 +376,35 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.tiles_x = (unsigned)((cam->hsize + 7) / 8);
     P.n_items = (unsigned long long)P.tiles_x * ((P.rows + 3) / 4) * 32ull;
     P.full_frame = full_frame ? 1 : 0;
+    P.scale = s->wf_scale;
     P.out = d_rgb;
     P.out8 = d_rgba;
     P.counters = s->d_counters;
     if (stats) std::memset(stats, 0, sizeof *stats);
     if (P.rows == 0) return RTC_OK;
-    if (!use_megakernel()) {
-        int rc = render_wavefront(s, P, stream, stats);
-        if (rc != RTC_ERR_CAPACITY + 1000) return rc;  // queue overflow: redo the frame with the megakernel below
+    const size_t n_px = (size_t)(P.rows * cam->hsize);
+    if (s->tuned_pixels != n_px) {  // another frame size (or partition): measure again
+        s->tuned_pixels = n_px;
+        s->frames = 0;
+        s->best_ms[0] = s->best_ms[1] = -1.0f;
+    }
+    int which = forced_kernel();
+    if (which < 0) {
+        // first guess: the wavefront pays where rays recurse and the frame is big enough to amortise its launches
+        const int guess = (s->has_secondary && n_px >= (1u << 19)) ? 1 : 0;
+        if (s->frames < 4) which = (s->frames & 1) ? 1 - guess : guess;  // two frames each: the first one is cold
+        else which = (s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
+    }
+    s->frames++;
+    if (which == 1) {
+        rtc_stats local{};
+        int rc = render_wavefront(s, P, stream, &local);
+        if (rc != RTC_ERR_CAPACITY + 1000) {
+            if (rc == RTC_OK && (s->best_ms[1] < 0.0f || local.kernel_ms < s->best_ms[1])) s->best_ms[1] = local.kernel_ms;
+            if (stats) *stats = local;
+            return rc;
+        }
+        s->best_ms[1] = 1e30f;  // queue overflow: this scene stays with the megakernel; redo the frame below
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
@@ -378,6 +425,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         stats->launches = 1;
         stats->shadow_rays_culled = c[5];
     }
+    if (s->best_ms[0] < 0.0f || ms < s->best_ms[0]) s->best_ms[0] = ms;
     if (c[4]) {
         char buf[160];
         std::snprintf(buf, sizeof buf,

@@ -147,6 +147,35 @@ def test_empty_world_and_no_lights(pkg, oracle):
     assert not img.pixels.any() and img.stats.shadow_rays == 0
 
 
+@pytest.mark.parametrize("name", ["smoke", "cover", "fresnel", "dragons"])
+def test_megakernel_and_wavefront_are_bit_identical(pkg, name):
+    """The two kernels add the same terms weight x lighting() to a pixel as exact integers, so they agree bit for
+    bit (and the library may pick whichever is faster for a scene without changing a single pixel)."""
+    from tests.golden import make_golden
+    if name == "smoke":
+        text, assets, (w, h) = scenes.SMOKE_SCENE, "", (160, 96)
+    else:
+        s = scenes.shipped_scene(name)
+        if s is None:
+            pytest.skip("reference assets not staged")
+        text, assets = s
+        w, h = make_golden.SIZES[name]
+        w, h = 3 * w, 3 * h
+    info = pkg.parse_scene(text, assets, w, h)
+    out = {}
+    try:
+        for k in ("mega", "wave"):
+            os.environ["RTC_KERNEL"] = k
+            c = info.camera.render(info.world)
+            out[k] = (c.pixels.copy(), c.stats.as_dict())
+    finally:
+        os.environ.pop("RTC_KERNEL", None)
+    assert out["mega"][1]["launches"] == 1 and out["wave"][1]["launches"] > 1
+    assert np.array_equal(out["mega"][0], out["wave"][0])
+    for key in ("primary", "shadow", "secondary", "shadow_culled"):
+        assert out["mega"][1][key] == out["wave"][1][key]
+
+
 def test_errors(pkg):
     with pytest.raises(pkg.RtcError):
         pkg.World(b"\0" * 512)
