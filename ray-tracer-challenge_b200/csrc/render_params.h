@@ -69,8 +69,6 @@ enum {
 struct WaveParams {
     DCamera cam;
     int max_depth, level;
-    int inline_shadows;  // rays of this level trace the shadow rays of their own hit (no hit records)
-    int shadow_stage;    // this launch runs the shadow queries of the previous level's hit records
     unsigned int tile_rows, part, n_parts;
     unsigned long long rows, n_pixels;  // of this partition
     const WRay* rays_in;   // rays of `level` (level 0: NULL, generated from the camera)

@@ -266,29 +266,7 @@ wave_kernel(DScene S, WaveParams W) {
                 }
             }
             // ---- hit record for the shadow queries of the next launch (shadeHit, world.zig:89-96) ---
-            if (W.inline_shadows) {
-                // the lane traces the shadow rays of its own hit, light after light (all lanes of the warp are at
-                // the same light at the same time), and adds weight x surface once.  Level 0 STORES: every pixel
-                // has exactly one primary ray, so this also initialises the accumulators (no memset, no atomics).
-                V3 over = point + normal * 1e-5;
-                V3 surface = v3(0, 0, 0);
-#pragma unroll 1
-                for (int li = 0; li < S.n_lights; li++)
-                    surface = surface + wf_light<MESH>(S, over, normal, q.d, color, mat, li, hit, stack, &err, n_culled);
-                unsigned hm = __ballot_sync(0xffffffffu, hit);
-                if (lane == 0 && hm) atomicAdd(C + WC_NHITS + level, (unsigned long long)__popc(hm));
-                if (live) {
-                    if (level == 0) {
-                        V3 c = surface * rw;
-                        double v[3] = {c.x * W.scale, c.y * W.scale, c.z * W.scale};
-#pragma unroll
-                        for (int k = 0; k < 3; k++)
-                            W.acc[3ll * pix + k] = (hit && fabs(v[k]) < 9.0e18) ? __double2ll_rn(v[k]) : 0ll;
-                    } else if (hit) {
-                        wf_add(W.acc, pix, surface * rw, W.scale);
-                    }
-                }
-            } else if (S.n_lights > 0) {
+            if (S.n_lights > 0) {
                 unsigned long long slot = wf_reserve(hit, C + WC_NHITS + level, W.cap, lane, lt_mask, &err);
                 if (slot != ~0ull) {
                     V3 over = point + normal * 1e-5;
@@ -352,7 +330,7 @@ wave_kernel(DScene S, WaveParams W) {
     }
 
     // ================= shadow queries of the previous level's hits: isShadowed + lighting ================
-    if (W.shadow_stage && level > 0 && S.n_lights > 0) {
+    if (level > 0 && S.n_lights > 0) {
         const unsigned long long L = (unsigned long long)S.n_lights;
         unsigned long long n_hits = C[WC_NHITS + level - 1] < W.cap ? C[WC_NHITS + level - 1] : W.cap;
         const unsigned long long n_tasks = n_hits * L;

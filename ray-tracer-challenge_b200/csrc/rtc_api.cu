@@ -234,16 +234,6 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     return RTC_OK;
 }
 
-// RTC_WF_INLINE: recursion levels whose shadow rays are traced inline by the lane that found the hit (default 0:
-// measured slower than separate shadow tasks on every config but skybox 4K; kept as a knob).
-static int wf_inline_levels() {
-    static const int v = [] {
-        const char* e = std::getenv("RTC_WF_INLINE");
-        return e ? std::atoi(e) : 0;
-    }();
-    return v;
-}
-
 // Grows (never shrinks) the wavefront buffers of a scene for a partition of n_pixels pixels.
 static int ensure_wavefront(rtc_scene* s, size_t n_pixels) {
     if (!s->wf_counters) CUDA_TRY(cudaMalloc(&s->wf_counters, WC_COUNT * sizeof(unsigned long long)));
@@ -290,17 +280,12 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
     W.counters = s->wf_counters;
     CUDA_TRY(cudaMemsetAsync(s->wf_counters, 0, WC_COUNT * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
-    // levels below wf_inline_levels() trace the shadow rays of a hit in the lane that found it; level 0 then
-    // initialises the accumulators itself
-    const int inl = wf_inline_levels();
-    if (inl < 1) CUDA_TRY(cudaMemsetAsync(s->wf_acc, 0, n_pixels * 3 * sizeof(long long), stream));
+    CUDA_TRY(cudaMemsetAsync(s->wf_acc, 0, n_pixels * 3 * sizeof(long long), stream));
     // without reflective / transparent materials no ray beyond level 0 can exist: level 0 + its shadows
     const int depth = s->has_secondary ? P.max_depth : 0;
-    const int n_launch = depth + ((depth < inl) ? 1 : 2);
+    const int n_launch = depth + 2;  // levels 0..depth, + the shadow queries of the last level's hits
     for (int level = 0; level < n_launch; level++) {
         W.level = level;
-        W.inline_shadows = level < inl;
-        W.shadow_stage = level > 0 && (level - 1) >= inl;
         W.rays_in = s->wf_rays[level & 1];
         W.rays_out = s->wf_rays[(level + 1) & 1];
         W.hits_in = s->wf_hits[(level + 1) & 1];
