@@ -87,6 +87,8 @@ struct DScene {
     int32_t n_lights, n_prims, n_meshes, n_csg;
     int32_t n_leaves, bvh_max_depth;
     float world_abs[3];  // max finite |coordinate| of any world pre-test box per axis (f32 slab error bound)
+    int32_t ri_all_one;  // every material has refractive_index == 1.0: n1 = n2 = 1 whatever the containers are
+    int32_t pad_ri[3];
     int32_t stack_cap;   // entries per thread of the shared-memory BVH traversal stack (bvh_max_depth + 2)
 };
 

@@ -249,7 +249,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_N2) = 1.0;
                 // n1/n2 only reach a result through refractedColor / schlick, both gated on
                 // transparency (world.zig:101-102, :178)
-                if (M.transparency != 0.0) state = ST_CONTAINERS;
+                // ... and when every material of the scene has refractive index 1.0 (dragons.json's glass boxes),
+                // n1 = n2 = 1.0 whatever the containers list holds (world.zig:236-254): the walk is skipped.
+                if (M.transparency != 0.0 && !S.ri_all_one) state = ST_CONTAINERS;
                 else state = S.n_lights > 0 ? ST_SHADOW : -1;  // no lights: straight to the children below
             }
         } else if (state == ST_CONTAINERS) {

@@ -239,7 +239,8 @@ wave_kernel(DScene S, WaveParams W) {
             // ---- n1 / n2 (world.zig:229-255): only reach a result through refractedColor / schlick, both
             //      gated on transparency (world.zig:101-102, :178) -> second query for those lanes only
             double n1 = 1.0, n2 = 1.0;
-            const bool transp = hit && transparency != 0.0;
+            // (skipped when every material has refractive index 1.0: n1 = n2 = 1.0 whatever the list holds)
+            const bool transp = hit && transparency != 0.0 && !S.ri_all_one;
             if (__any_sync(0xffffffffu, transp)) {
                 Query c;
                 c.mode = Q_CONTAINERS;

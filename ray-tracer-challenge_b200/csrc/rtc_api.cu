@@ -204,8 +204,11 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     s->grid = prop.multiProcessorCount * per_sm;
     // wavefront kernels: no parked state, only the traversal stacks
     s->wf_smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
-    for (const rtc_material& m : hs.materials)
+    d.ri_all_one = 1;
+    for (const rtc_material& m : hs.materials) {
         if (m.reflective != 0.0 || m.transparency != 0.0) s->has_secondary = true;
+        if (m.refractive_index != 1.0) d.ri_all_one = 0;
+    }
     int wf_per_sm = 0;
     e = (cudaError_t)(d.n_meshes > 0 ? occupancy_wave_mesh(&wf_per_sm, s->wf_smem) : occupancy_wave_analytic(&wf_per_sm, s->wf_smem));
     if (e != cudaSuccess) return bail(e, "occupancy query (wavefront)");
