@@ -24,7 +24,10 @@ def main():
     ap.add_argument("--all", action="store_true")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--only", default="")
+    ap.add_argument("--kernel", default="", help="pin RTC_KERNEL=mega|wave (default: the library's measured choice)")
     args = ap.parse_args()
+    if args.kernel:
+        os.environ["RTC_KERNEL"] = args.kernel
     import torch
     pkg = importlib.import_module("ray-tracer-challenge_b200")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")

@@ -21,7 +21,10 @@ def main():
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--parts", default="1,2,4,8")
+    ap.add_argument("--kernel", default="", help="pin RTC_KERNEL=mega|wave")
     a = ap.parse_args()
+    if a.kernel:
+        os.environ["RTC_KERNEL"] = a.kernel
     import torch
     pkg = importlib.import_module("ray-tracer-challenge_b200")
     text, assets = scenes.shipped_scene(a.scene)
@@ -33,7 +36,7 @@ def main():
         per = []
         for r in range(min(n, 8)):
             best = 1e9
-            for _ in range(4):
+            for _ in range(8):
                 if not a.no_flush:
                     flush.zero_()
                 torch.cuda.synchronize()
