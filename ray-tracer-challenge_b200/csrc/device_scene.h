@@ -24,7 +24,7 @@ static_assert(sizeof(DTri) == 80, "DTri must be 80 bytes");
 // DTri records.  An unused child has an inverted box (lo=+inf, hi=-inf) and n = 0, c = -1.
 struct BvhNode {
     float lo0[3], hi0[3], lo1[3], hi1[3];
-    int32_t c0, c1, n0, n1;
+    int32_t c0, c1, n0, n1;  // c: inner node index, or ~((first triangle << 3) | count) for a leaf child; n: its triangle count
 };
 static_assert(sizeof(BvhNode) == 64, "BvhNode must be 64 bytes");
 

@@ -75,8 +75,10 @@ __device__ __forceinline__ void cont_add(Query& q, int leaf, int n, const double
 // (rounding of o and d to f32, the f32 reciprocal, the rounded product o*(1/d), one fused multiply-add:
 // together below 2^-22 (|b| + 2|o|) |1/d|; the bound used keeps a factor 2 in hand).
 struct FRay {
-    float cx, cy, cz;  // -o * (1/d): the slab parameter of plane b is fma(b, 1/d, c)
-    float ix, iy, iz, ex, ey, ez;
+    float ix, iy, iz;  // 1/d
+    // -o * (1/d) -+ the error bound: the slab parameter of plane b is fma(b, 1/d, c); with the bound folded into
+    // the constant (rounded outward), the near planes give a lower and the far planes an upper bound directly
+    float nx, ny, nz, fx, fy, fz;
 };
 __device__ __forceinline__ float finv(double d) {
     // d == 0 (or below f32 range) gives +-inf: clamp, so that (b - o) == 0 yields 0 and not NaN
@@ -87,24 +89,30 @@ __device__ __forceinline__ FRay make_fray(V3 o, V3 d, float bax, float bay, floa
     FRay r;
     float ox = (float)o.x, oy = (float)o.y, oz = (float)o.z;
     r.ix = finv(d.x), r.iy = finv(d.y), r.iz = finv(d.z);
-    // finite by construction when o is (|1/d| <= FLT_MAX); an overflowing product saturates, and the
-    // error term below is then FLT_MAX too, which leaves that axis unconstrained
-    r.cx = fminf(fmaxf(-ox * r.ix, -FLT_MAX), FLT_MAX);
-    r.cy = fminf(fmaxf(-oy * r.iy, -FLT_MAX), FLT_MAX);
-    r.cz = fminf(fmaxf(-oz * r.iz, -FLT_MAX), FLT_MAX);
+    // finite by construction when o is (|1/d| <= FLT_MAX); an overflowing product saturates towards its own
+    // sign, which keeps the comparison against the (finite) query range right
+    float cx = fminf(fmaxf(-ox * r.ix, -FLT_MAX), FLT_MAX);
+    float cy = fminf(fmaxf(-oy * r.iy, -FLT_MAX), FLT_MAX);
+    float cz = fminf(fmaxf(-oz * r.iz, -FLT_MAX), FLT_MAX);
     const float k = 4.76837158e-7f;  // 2^-21
-    r.ex = fminf(FLT_MAX, k * (bax + 2.0f * fabsf(ox)) * fabsf(r.ix));
-    r.ey = fminf(FLT_MAX, k * (bay + 2.0f * fabsf(oy)) * fabsf(r.iy));
-    r.ez = fminf(FLT_MAX, k * (baz + 2.0f * fabsf(oz)) * fabsf(r.iz));
+    float ex = fminf(FLT_MAX, k * (bax + 2.0f * fabsf(ox)) * fabsf(r.ix));
+    float ey = fminf(FLT_MAX, k * (bay + 2.0f * fabsf(oy)) * fabsf(r.iy));
+    float ez = fminf(FLT_MAX, k * (baz + 2.0f * fabsf(oz)) * fabsf(r.iz));
+    // (c - e) rounded down, (c + e) rounded up; a saturated e leaves the axis unconstrained (-inf / +inf, or a
+    // NaN out of inf - inf in the fma below, which fminf / fmaxf drop)
+    r.nx = __fsub_rd(cx, ex), r.ny = __fsub_rd(cy, ey), r.nz = __fsub_rd(cz, ez);
+    r.fx = __fadd_ru(cx, ex), r.fy = __fadd_ru(cy, ey), r.fz = __fadd_ru(cz, ez);
     return r;
 }
 __device__ __forceinline__ bool fbox(const FRay& r, float lx, float ly, float lz, float hx, float hy, float hz,
                                      float t_lo, float t_hi, float& tnear) {
-    float ax = __fmaf_rn(lx, r.ix, r.cx), bx = __fmaf_rn(hx, r.ix, r.cx);
-    float ay = __fmaf_rn(ly, r.iy, r.cy), by = __fmaf_rn(hy, r.iy, r.cy);
-    float az = __fmaf_rn(lz, r.iz, r.cz), bz = __fmaf_rn(hz, r.iz, r.cz);
-    float tn = fmaxf(fmaxf(fminf(ax, bx) - r.ex, fminf(ay, by) - r.ey), fmaxf(fminf(az, bz) - r.ez, t_lo));
-    float tf = fminf(fminf(fmaxf(ax, bx) + r.ex, fmaxf(ay, by) + r.ey), fminf(fmaxf(az, bz) + r.ez, t_hi));
+    // the plane the ray enters through is lo where it travels in +axis, hi where it travels in -axis
+    const bool sx = r.ix < 0.0f, sy = r.iy < 0.0f, sz = r.iz < 0.0f;
+    float ax = __fmaf_rn(sx ? hx : lx, r.ix, r.nx), bx = __fmaf_rn(sx ? lx : hx, r.ix, r.fx);
+    float ay = __fmaf_rn(sy ? hy : ly, r.iy, r.ny), by = __fmaf_rn(sy ? ly : hy, r.iy, r.fy);
+    float az = __fmaf_rn(sz ? hz : lz, r.iz, r.nz), bz = __fmaf_rn(sz ? lz : hz, r.iz, r.fz);
+    float tn = fmaxf(fmaxf(ax, ay), fmaxf(az, t_lo));
+    float tf = fminf(fminf(bx, by), fminf(bz, t_hi));
     tnear = tn;
     return tn <= tf;
 }
@@ -282,12 +290,11 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
         while (node >= 0) {
             const float4* np = reinterpret_cast<const float4*>(S.bvh + node);
             float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2);
-            int4 ci = __ldg(reinterpret_cast<const int4*>(np + 3));
+            int2 ci = __ldg(reinterpret_cast<const int2*>(np + 3));  // child references, leaves pre-encoded (scene_build.cpp)
             float n0, n1;
             bool h0 = fbox(T.r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, t_lo, t_hi, n0);
             bool h1 = fbox(T.r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, t_lo, t_hi, n1);
-            int c0 = ci.z > 0 ? ~((ci.x << 3) | ci.z) : ci.x;
-            int c1 = ci.w > 0 ? ~((ci.y << 3) | ci.w) : ci.y;
+            const int c0 = ci.x, c1 = ci.y;
             if (h0 && h1) {
                 bool swap = n1 < n0;  // nearer child first: it can shrink t_hi before the other is opened
                 int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;

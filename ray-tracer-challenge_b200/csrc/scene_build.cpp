@@ -279,9 +279,11 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         mesh_world_box(hs.transforms[(size_t)m.transform], m);
         int32_t node_base = (int32_t)hs.bvh.size(), tri_base = (int32_t)hs.tris.size();
         for (BvhNode n : b.nodes) {
-            if (n.n0 > 0) n.c0 += tri_base;
+            // child references as the traversal holds them: inner node index >= 0, or a leaf as
+            // ~((first triangle << 3) | count) (rt_trace.cuh mesh_inner / mesh_leaf)
+            if (n.n0 > 0) n.c0 = ~(((n.c0 + tri_base) << 3) | n.n0);
             else if (n.c0 >= 0) n.c0 += node_base;
-            if (n.n1 > 0) n.c1 += tri_base;
+            if (n.n1 > 0) n.c1 = ~(((n.c1 + tri_base) << 3) | n.n1);
             else if (n.c1 >= 0) n.c1 += node_base;
             hs.bvh.push_back(n);
         }
