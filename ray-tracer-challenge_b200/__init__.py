@@ -58,6 +58,11 @@ class rtc_stats(ctypes.Structure):
 EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
            "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free"]
+# include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
+RENDERER_EXPORTS = ["startInitRenderer", "tryFinishInitRenderer", "initRendererIsOk", "initRendererGetPixels",
+                    "initRendererGetWidth", "initRendererGetHeight", "initRendererGetErr", "deinitRenderer",
+                    "startRender", "tryFinishRender", "rotateCamera", "moveCamera", "rtcRendererSetAssetDir",
+                    "rtcRendererLastStats"]
 
 
 def lib():
@@ -92,6 +97,22 @@ def lib():
     L.rtc_host_free.argtypes = [vp]
     L.rtc_host_free.restype = None
     L.rtc_camera_look_at.argtypes = [ctypes.POINTER(rtc_camera)] + [ctypes.POINTER(ctypes.c_double)] * 3
+    L.startInitRenderer.argtypes = [cp, ctypes.c_size_t]
+    L.startInitRenderer.restype = None
+    for name in ("tryFinishInitRenderer", "initRendererIsOk", "tryFinishRender"):
+        getattr(L, name).restype = ctypes.c_bool
+    L.initRendererGetPixels.restype = vp
+    L.initRendererGetWidth.restype = ctypes.c_size_t
+    L.initRendererGetHeight.restype = ctypes.c_size_t
+    L.initRendererGetErr.restype = cp
+    for name in ("deinitRenderer", "startRender"):
+        getattr(L, name).restype = None
+    for name in ("rotateCamera", "moveCamera"):
+        getattr(L, name).argtypes = [ctypes.c_double]
+        getattr(L, name).restype = None
+    L.rtcRendererSetAssetDir.argtypes = [cp]
+    L.rtcRendererSetAssetDir.restype = None
+    L.rtcRendererLastStats.argtypes = [ctypes.POINTER(rtc_stats)]
     _lib = L
     return L
 
@@ -281,3 +302,46 @@ def parse_scene(json_text, asset_dir="", width=0, height=0, device=0):
 def parse_scene_file(path, asset_dir="", width=0, height=0, device=0):
     with open(path) as f:
         return parse_scene(f.read(), asset_dir, width, height, device)
+
+
+class Renderer:
+    """The reference's global Renderer (lib.zig:65-191, 194) driven the way www/index.js drives it: start, poll,
+    read the library-owned RGBA8 buffer, orbit, render again.  One per process."""
+
+    def __init__(self, json_text, asset_dir=".", n_threads=0, poll_s=0.0005):
+        import time
+        L = lib()
+        self._poll = poll_s
+        L.rtcRendererSetAssetDir(asset_dir.encode())
+        self._text = json_text.encode()  # must outlive the init worker (lib.zig:233: the pointer is read there)
+        L.startInitRenderer(self._text, n_threads)
+        while not L.tryFinishInitRenderer():
+            time.sleep(poll_s)
+        if not L.initRendererIsOk():
+            raise RtcError(RTC_ERR_PARSE, L.initRendererGetErr().decode(errors="replace"))
+        self.width, self.height = int(L.initRendererGetWidth()), int(L.initRendererGetHeight())
+        buf = (ctypes.c_uint8 * (4 * self.width * self.height)).from_address(L.initRendererGetPixels())
+        self.pixels = np.frombuffer(buf, dtype=np.uint8).reshape(self.height, self.width, 4)  # the library's buffer
+
+    def render(self):
+        """startRender + tryFinishRender until done -> the (library-owned) [H,W,4] uint8 view."""
+        import time
+        L = lib()
+        L.startRender()
+        while not L.tryFinishRender():
+            time.sleep(self._poll)
+        return self.pixels
+
+    def rotate_camera(self, angle):
+        lib().rotateCamera(angle)
+
+    def move_camera(self, distance):
+        lib().moveCamera(distance)
+
+    def stats(self):
+        st = rtc_stats()
+        return st if lib().rtcRendererLastStats(ctypes.byref(st)) == 0 else None
+
+    def close(self):
+        self.pixels = None
+        lib().deinitRenderer()

@@ -19,6 +19,22 @@ def test_library_exports_every_declared_symbol(pkg):
     L = pkg.lib()
     for name in declared:
         assert hasattr(L, name), name
+    # include/rtc_renderer.h: the reference's own twelve exports (lib.zig:233-309), same names
+    hdr = open(os.path.join(scenes.ROOT, "include", "rtc_renderer.h")).read()
+    hdr = hdr[hdr.index('extern "C"'):]
+    declared = set(re.findall(r"\b([a-zA-Z]+)\s*\((?:void|const|double|size_t)", hdr))
+    assert declared == set(pkg.RENDERER_EXPORTS), declared ^ set(pkg.RENDERER_EXPORTS)
+    for name in ("startInitRenderer", "tryFinishInitRenderer", "initRendererIsOk", "initRendererGetPixels",
+                 "initRendererGetWidth", "initRendererGetHeight", "initRendererGetErr", "deinitRenderer",
+                 "startRender", "tryFinishRender", "rotateCamera", "moveCamera"):
+        assert name in declared and hasattr(L, name), name
+
+
+def test_renderer_init_reports_errors(pkg):
+    """lib.zig:216-231: a scene that does not parse ends in initRendererIsOk() == false + a message, not a crash."""
+    with pytest.raises(pkg.RtcError) as e:
+        pkg.Renderer("{not json")
+    assert str(e.value)
 
 
 def parse_header(blob):
