@@ -317,6 +317,20 @@ def main():
         assert np.array_equal(host, host_pageable), "pinned and pageable canvases differ"
     sampler.stop_flag = True
     sampler.join()
+    # what the e2e leg is bounded by: a plain DMA copy of one frame, device -> page-locked host memory
+    d2h_ms = None
+    if rank == 0:
+        src = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, device=dev)
+        dst = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64).pin_memory()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e9
+        for _ in range(6):
+            c0.record()
+            dst.copy_(src, non_blocking=True)
+            c1.record()
+            torch.cuda.synchronize()
+            best = min(best, c0.elapsed_time(c1))
+        d2h_ms = best
 
     t = torch.tensor([dev_ms, e_secs], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(rays), float(e_rays), float(launches)], dtype=torch.float64, device=dev)
@@ -340,7 +354,10 @@ def main():
                     "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24),
                     "canvas": "page-locked host memory (rtc_host_alloc): the kernel stores finished pixels into it over "
                               "PCIe while rendering" if world == 1 else "rank 0 copies the assembled frame to pinned memory",
-                    "pageable_canvas_ms_per_step": (1e3 * p_secs / args.steps) if p_secs else None},
+                    "pageable_canvas_ms_per_step": (1e3 * p_secs / args.steps) if p_secs else None,
+                    "d2h_copy_floor_ms": d2h_ms,
+                    "d2h_copy_floor": "one cudaMemcpy of the f64 frame (49.8 MB) into pinned memory on this box: the e2e step "
+                                      "cannot be shorter than max(kernel, this)"},
             "gpu_launches": launches_all,
             "rays_per_frame": rays_all / args.steps,
             # shadow rays the reference casts (and `value` counts) but this renderer does not trace because the
