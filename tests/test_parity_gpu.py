@@ -243,3 +243,42 @@ def test_renderer_twin_of_lib_zig(pkg):
         assert (diff <= 1).mean() > 0.999  # `from` differs in the last bits between numpy and the C++ mirror
     finally:
         r.close()
+
+
+@pytest.mark.parametrize("name,w,h", [("fresnel", 600, 600), ("cover", 1920, 1080), ("teapot", 1920, 1080),
+                                      ("dragons", 1920, 1080), ("csg", 3840, 2160), ("skybox", 3840, 2160)])
+def test_baseline_config_full_size(pkg, oracle, name, w, h):
+    """BASELINE.json's configs at their FULL sizes: the oracle renders evenly spaced row bands of the full-size
+    frame (a few seconds of CPU), the GPU the whole frame; plus the size-independent properties — the union of
+    three interleaved partitions is the frame, the RGBA8 twin is clamp() of the f64 frame, the ray counts of the
+    partitions add up."""
+    s = scenes.shipped_scene(name)
+    if s is None:
+        pytest.skip("reference assets not staged (assets/_ref)")
+    text, assets = s
+    info = pkg.parse_scene(text, assets, w, h)
+    canvas = info.camera.render(info.world)
+    assert np.isfinite(canvas.pixels).all() and canvas.stats.primary_rays == w * h
+    ref = oracle.OracleScene(json_text=text, asset_dir=assets, width=w, height=h)
+    bands, rows, n_px, n_ok = 6, 4, 0, 0
+    for b in range(bands):
+        y0 = int((b + 0.5) * h / bands) - rows // 2
+        want, _ = ref.render(y0=y0, y1=y0 + rows)
+        d = np.abs(canvas.pixels[y0:y0 + rows] - want[y0:y0 + rows]).max(axis=2)
+        ok = d <= TOL
+        q = np.abs(canvas.to_image()[y0:y0 + rows].astype(int) - oracle.quantise(want[y0:y0 + rows]).astype(int)).max(axis=2)
+        assert q[ok].max() <= 1
+        n_px += ok.size
+        n_ok += int(ok.sum())
+    print("%s %dx%d: %d of %d oracle pixels within %.0e" % (name, w, h, n_ok, n_px, TOL))
+    assert n_ok >= 0.999 * n_px
+    acc = np.zeros_like(canvas.pixels)
+    rays = 0
+    for part in range(3):
+        c = info.camera.render(info.world, partition=(8, part, 3), out=acc)
+        rays += c.stats.rays
+    assert np.array_equal(acc, canvas.pixels) and rays == canvas.stats.rays
+    rgba, _ = info.camera.render_rgba8(info.world)
+    assert np.array_equal(rgba[..., :3], oracle.quantise(canvas.pixels)) and (rgba[..., 3] == 255).all()
+    info.world.close()
+    ref.close()
