@@ -9,12 +9,12 @@ EXTRA ?=
 NVFLAGS ?= $(EXTRA) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=$(FMAD) -Xcompiler -fPIC,-Wall
 SRC := $(CSRC)/render_mesh.cu $(CSRC)/render_analytic.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
        $(CSRC)/host/scene.cpp $(CSRC)/host/scene_parser.cpp $(CSRC)/host/obj.cpp $(CSRC)/host/images.cpp \
-       $(CSRC)/host/flatten.cpp $(CSRC)/rtc_renderer.cpp
+       $(CSRC)/host/flatten.cpp $(CSRC)/rtc_renderer.cpp $(CSRC)/host/image_write.cpp
 HDR := $(wildcard $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh $(CSRC)/host/*.hpp include/*.h)
 
 OUT ?= $(PKG)/librtc_b200.so
 
-all: $(OUT) oracle
+all: $(OUT) oracle tools/peaks
 
 # one object per source so that `make -j` compiles the kernel instantiations in parallel
 OBJDIR ?= build/$(notdir $(basename $(OUT)))
@@ -27,6 +27,10 @@ $(OUT): $(OBJ)
 
 oracle:
 	$(MAKE) -C oracle all
+
+# measured FP64 / FP32 FMA peak and L2 copy bandwidth (denominators of the ALU / L2 rooflines)
+tools/peaks: tools/peaks.cu
+	$(NVCC) -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -o $@ $<
 
 clean:
 	rm -f $(PKG)/librtc_b200.so

@@ -97,6 +97,12 @@ uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part);
 int rtc_load_scene_json(const char* json_text, const char* asset_dir, long width, long height,
                         void** blob_out, size_t* nbytes_out, rtc_camera* cam_out);
 void rtc_blob_free(void* blob);
+/* The step after the render.  rtc_canvas_ppm: Canvas.ppm (canvas.zig:181-254) of an f64 frame, character for
+ * character (clamp() quantisation, lines broken before column 70); *text_out is NUL-terminated, release it with
+ * rtc_blob_free.  rtc_write_png: the rgb24 PNG main.zig:95-99 writes from Canvas.toImage (canvas.zig:150-176),
+ * from the RGBA8 frame of rtc_render_rgba8 (alpha dropped). */
+int rtc_canvas_ppm(const double* rgb, uint64_t width, uint64_t height, char** text_out, size_t* nbytes_out);
+int rtc_write_png(const char* path, const uint8_t* rgba, uint64_t width, uint64_t height);
 /* lib.zig:166-190 camera orbit: rebuilds cam->inverse from from/to/up (matrix.zig:54-67). */
 int rtc_camera_look_at(rtc_camera* cam, const double from[3], const double to[3], const double up[3]);
 

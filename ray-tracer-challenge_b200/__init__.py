@@ -57,7 +57,7 @@ class rtc_stats(ctypes.Structure):
 # every symbol include/rtc_b200.h declares
 EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
-           "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free"]
+           "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png"]
 # include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
 RENDERER_EXPORTS = ["startInitRenderer", "tryFinishInitRenderer", "initRendererIsOk", "initRendererGetPixels",
                     "initRendererGetWidth", "initRendererGetHeight", "initRendererGetErr", "deinitRenderer",
@@ -97,6 +97,8 @@ def lib():
     L.rtc_host_free.argtypes = [vp]
     L.rtc_host_free.restype = None
     L.rtc_camera_look_at.argtypes = [ctypes.POINTER(rtc_camera)] + [ctypes.POINTER(ctypes.c_double)] * 3
+    L.rtc_canvas_ppm.argtypes = [vp, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_size_t)]
+    L.rtc_write_png.argtypes = [cp, vp, ctypes.c_uint64, ctypes.c_uint64]
     L.startInitRenderer.argtypes = [cp, ctypes.c_size_t]
     L.startInitRenderer.restype = None
     for name in ("tryFinishInitRenderer", "initRendererIsOk", "tryFinishRender"):
@@ -186,10 +188,21 @@ class Canvas:
         return np.clip(np.nan_to_num(r, nan=0.0), 0, 255).astype(np.uint8)
 
     def ppm(self):
-        """Canvas.ppm (canvas.zig:181-254) without the 70-column wrapping (plain P3)."""
+        """Canvas.ppm (canvas.zig:181-254), character for character (lines broken before column 70)."""
+        L = lib()
+        px = np.ascontiguousarray(self.pixels, dtype=np.float64)
+        text, n = ctypes.c_void_p(), ctypes.c_size_t()
+        _check(L.rtc_canvas_ppm(px.ctypes.data, self.width, self.height, ctypes.byref(text), ctypes.byref(n)))
+        try:
+            return ctypes.string_at(text, n.value).decode()
+        finally:
+            L.rtc_blob_free(text)
+
+    def save_png(self, path):
+        """main.zig:95-99: canvas.toImage() written as an rgb24 PNG."""
         img = self.to_image()
-        rows = [" ".join(str(v) for v in row.reshape(-1)) for row in img]
-        return "P3\n%d %d\n255\n%s\n" % (self.width, self.height, "\n".join(rows))
+        rgba = np.concatenate([img, np.full(img.shape[:2] + (1,), 255, dtype=np.uint8)], axis=2)
+        _check(lib().rtc_write_png(str(path).encode(), np.ascontiguousarray(rgba).ctypes.data, self.width, self.height))
 
 
 class World:

@@ -119,3 +119,46 @@ def test_oracle_default_world_kat(oracle):
     img, counts = s.render(threads=2)
     assert np.allclose(img[5, 5], [0.38066, 0.47583, 0.2855], atol=1e-5)
     assert counts["primary"] == 121
+
+
+def test_canvas_ppm_golden(pkg):
+    """canvas.zig:259-301: the reference's own two PPM vectors (clamping, and lines broken before column 70)."""
+    px = np.zeros((3, 5, 3))
+    px[0, 0, 0] = 1.5
+    px[1, 2, 1] = 0.5
+    px[2, 4] = (-0.5, 0.0, 1.0)
+    assert pkg.Canvas(px).ppm() == ("P3\n5 3\n255\n"
+                                    "255 0 0 0 0 0 0 0 0 0 0 0 0 0 0\n"
+                                    "0 0 0 0 0 0 0 128 0 0 0 0 0 0 0\n"
+                                    "0 0 0 0 0 0 0 0 0 0 0 0 0 0 255\n")
+    px = np.empty((2, 10, 3))
+    px[:] = (1, 0.8, 0.6)
+    row = ("255 204 153 255 204 153 255 204 153 255 204 153 255 204 153 255 204\n"
+           "153 255 204 153 255 204 153 255 204 153 255 204 153\n")
+    assert pkg.Canvas(px).ppm() == "P3\n10 2\n255\n" + row + row
+
+
+def test_png_round_trip(pkg, tmp_path):
+    """rtc_write_png (main.zig:95-99's rgb24 PNG) read back with nothing but zlib."""
+    import zlib
+    rng = np.random.default_rng(5)
+    px = rng.random((7, 13, 3)) * 1.2 - 0.1
+    c = pkg.Canvas(px)
+    path = tmp_path / "out.png"
+    c.save_png(path)
+    data = path.read_bytes()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, ihdr = 8, b"", None
+    while pos < len(data):
+        n, kind = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(kind + body)
+        if kind == b"IHDR":
+            ihdr = struct.unpack(">IIBBBBB", body)
+        elif kind == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert ihdr == (13, 7, 8, 2, 0, 0, 0)
+    raw = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(7, 1 + 13 * 3)
+    assert not raw[:, 0].any()
+    assert np.array_equal(raw[:, 1:].reshape(7, 13, 3), c.to_image())

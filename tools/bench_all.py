@@ -19,6 +19,36 @@ NATIVE = [("cubes", 0, 0), ("cylinders", 0, 0), ("reflection_and_refraction", 0,
           ("nefertiti", 0, 0), ("align_check", 0, 0), ("earth", 0, 0)]
 
 
+# algorithmic work per ray.  Analytic scenes: f64 flops (ray transform 56 + primitive test per
+# top-level leaf + 160 shading + 28 per pattern level); mesh scenes: BVH node + triangle bytes.
+FLOPS_PER_RAY = {"fresnel": 225.0, "cover": 1604.0}
+BYTES_PER_RAY = {"teapot": 992.0, "dragons": 1504.0}
+
+
+def roofline(name, rays_per_s):
+    """Fraction of the MEASURED peak (profiles/r1_alu_l2_peaks.json from tools/peaks, MEASURED_PEAKS.json) the
+    algorithmic work per ray amounts to; None for configs SURVEY.md gives no per-ray figure for."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        alu = json.load(open(os.path.join(root, "profiles", "r1_alu_l2_peaks.json")))
+    except OSError:
+        return None
+    if name in FLOPS_PER_RAY:
+        a = FLOPS_PER_RAY[name] * rays_per_s / 1e12
+        return {"bound": "fp64", "achieved": round(a, 3), "peak": alu["fp64_fma_tflops"], "unit": "TFLOP/s",
+                "frac": round(a / alu["fp64_fma_tflops"], 4), "model": "%g f64 flops/ray" % FLOPS_PER_RAY[name]}
+    if name in BYTES_PER_RAY:
+        a = BYTES_PER_RAY[name] * rays_per_s / 1e9
+        hbm = alu["hbm_copy_gbs"]
+        try:
+            hbm = json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbs"]
+        except (OSError, KeyError):
+            pass
+        return {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
+                "frac_of_l2_copy": round(a / alu["l2_copy_gbs"], 4), "model": "%g B/ray" % BYTES_PER_RAY[name]}
+    return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--all", action="store_true")
@@ -50,7 +80,8 @@ def main():
                 times.append(st.kernel_ms)
         times.sort()
         ms = times[len(times) // 2]
-        print(json.dumps({"scene": name, "width": cam.hsize, "height": cam.vsize, "kernel_ms": round(ms, 4),
+        roof = roofline(name, st.rays / (ms * 1e-3))
+        print(json.dumps({"roofline": roof, "scene": name, "width": cam.hsize, "height": cam.vsize, "kernel_ms": round(ms, 4),
                           "min_ms": round(times[0], 4), "rays": st.rays, "Mrays_s": round(st.rays / ms / 1e3, 1),
                           "primary": st.primary_rays, "shadow": st.shadow_rays, "secondary": st.secondary_rays, "shadow_culled": st.shadow_rays_culled,
                           "kernel": "megakernel" if st.launches == 1 else "wavefront (%d launches)" % st.launches, "setup_s": round(setup, 3), "checksum": float(buf.sum().item())}), flush=True)
