@@ -404,6 +404,10 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     CUDA_TRY(cudaStreamSynchronize(stream));
     float ms = 0;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+#ifdef RTC_TRIP_PROBE
+    std::fprintf(stderr, "trip probe: max trip %.1f us, trips %llu, > 50 us: %llu, > 20 us: %llu (kernel %.3f ms)\n", c[6] / 1965.0,
+                 c[7] & 0xffffffffull, (c[7] >> 32) & 0xffffull, c[7] >> 48, ms);
+#endif
     if (stats) {
         stats->primary_rays = c[1];
         stats->shadow_rays = c[2];
