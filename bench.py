@@ -61,6 +61,16 @@ def peaks():
         return 6650.0, "fallback"
 
 
+def l2_fraction(achieved_gbs):
+    """The same figure against the L2-resident copy bandwidth measured on a B200 by tools/peaks (committed)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_alu_l2_peaks.json")) as f:
+            l2 = float(json.load(f)["l2_copy_gbs"])
+        return {"l2_copy_peak": l2, "frac_of_l2_copy": achieved_gbs / l2}
+    except Exception:
+        return {}
+
+
 class ClockSampler(threading.Thread):
     """SM clock + throttle reasons sampled WHILE the timed region runs (NVML, ~1 kHz; falls back to
     nvidia-smi, ~20 Hz, when pynvml is missing)."""
@@ -368,7 +378,10 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
                          "model": "%d algorithmic B/ray (SURVEY.md 8d) x rays per launch / CUDA-event launch time; the "
-                                  "working set is L2-resident, so this is a node-fetch figure against the HBM peak" % BYTES_PER_RAY},
+                                  "working set is L2-resident (traffic = measured DRAM bytes per launch: ~1 %% of the "
+                                  "algorithmic bytes), so this is a node-fetch figure set against the HBM peak and may "
+                                  "exceed it; frac_of_l2_copy sets it against the measured L2-resident copy bandwidth" % BYTES_PER_RAY,
+                         **l2_fraction(achieved)},
             "clocks": sampler.summary(),
             "exchange": exchange,
             "scene_setup": {"parse_flatten_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "blob_bytes": len(blob)},
