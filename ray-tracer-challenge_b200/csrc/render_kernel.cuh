@@ -135,8 +135,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     // 8x4 pixel tiles, row-major tiles over the packed rows of this partition
                     unsigned long long tile = item >> 5;
                     unsigned in = (unsigned)(item & 31u);
-                    unsigned long long px = (tile % P.tiles_x) * 8ull + (in & 7u);
-                    unsigned long long pr = (tile / P.tiles_x) * 4ull + (in >> 3);
+                    unsigned long long px = (tile % P.tiles_x) * RTC_TILE_W + (in & (RTC_TILE_W - 1u));
+                    unsigned long long pr = (tile / P.tiles_x) * RTC_TILE_H + (in >> RTC_TILE_W_LOG2);
                     if (px < P.cam.hsize && pr < P.rows) {
                         unsigned long long y = ((pr / P.tile_rows) * P.n_parts + P.part) * P.tile_rows + pr % P.tile_rows;
                         // Camera.rayForPixel (camera.zig:64-76)

@@ -10,6 +10,15 @@ namespace rtc {
 #define RTC_BLOCK_THREADS 128  // threads per CTA of the render kernels
 #endif
 
+// The pixel tile one warp works on at a time: RTC_TILE_W x RTC_TILE_H = 32 pixels (megakernel only; the wavefront's
+// level-0 generation keeps 8x4).  log2 values.
+#ifndef RTC_TILE_W_LOG2
+#define RTC_TILE_W_LOG2 3
+#endif
+#define RTC_TILE_H_LOG2 (5 - RTC_TILE_W_LOG2)
+#define RTC_TILE_W (1u << RTC_TILE_W_LOG2)
+#define RTC_TILE_H (1u << RTC_TILE_H_LOG2)
+
 #define RTC_PARK_SLOTS 22  // doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*)
 
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)

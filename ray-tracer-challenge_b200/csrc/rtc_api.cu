@@ -361,8 +361,8 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.part = part->part;
     P.n_parts = part->n_parts;
     P.rows = rtc_partition_rows(cam->vsize, part);
-    P.tiles_x = (unsigned)((cam->hsize + 7) / 8);
-    P.n_items = (unsigned long long)P.tiles_x * ((P.rows + 3) / 4) * 32ull;
+    P.tiles_x = (unsigned)((cam->hsize + RTC_TILE_W - 1) / RTC_TILE_W);
+    P.n_items = (unsigned long long)P.tiles_x * ((P.rows + RTC_TILE_H - 1) / RTC_TILE_H) * 32ull;
     P.full_frame = full_frame ? 1 : 0;
     P.scale = s->wf_scale;
     P.out = d_rgb;
