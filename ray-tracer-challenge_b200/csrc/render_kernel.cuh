@@ -136,7 +136,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     unsigned long long tile = item >> 5;
                     unsigned in = (unsigned)(item & 31u);
                     unsigned long long px = (tile % P.tiles_x) * RTC_TILE_W + (in & (RTC_TILE_W - 1u));
-                    unsigned long long pr = (tile / P.tiles_x) * RTC_TILE_H + (in >> RTC_TILE_W_LOG2);
+                    unsigned long long trow = tile / P.tiles_x;
+                    if (P.row_stride != 1) {  // strided order of the row groups (render_params.h), 32-bit arithmetic
+                        const unsigned t = (unsigned)trow, g = t / P.row_group;
+                        if (g < P.n_row_groups)
+                            trow = (unsigned)(((unsigned long long)g * P.row_stride) % P.n_row_groups) * P.row_group + t % P.row_group;
+                    }
+                    unsigned long long pr = trow * RTC_TILE_H + (in >> RTC_TILE_W_LOG2);
                     if (px < P.cam.hsize && pr < P.rows) {
                         unsigned long long y = ((pr / P.tile_rows) * P.n_parts + P.part) * P.tile_rows + pr % P.tile_rows;
                         // Camera.rayForPixel (camera.zig:64-76)

@@ -34,6 +34,11 @@ struct RenderParams {
     unsigned long long rows;       // rows of this partition
     unsigned long long n_items;    // tiles_x * tiles_y * 32 work items (some fall outside the frame)
     unsigned int tiles_x;
+    // Groups of tile rows are handed out in the order (k * row_stride) % n_row_groups, k = 0, 1, ... (row_stride coprime
+    // to n_row_groups, about 0.38 of it; the rows past the last full group keep their place): consecutive work is spread over the frame, so cheap and expensive regions of
+    // the picture are rendered side by side and pixels reach the canvas at an even rate (a canvas in host memory is
+    // written over PCIe while the kernel runs; a burst of cheap rows at the end would have to wait for the link).
+    unsigned int row_stride, n_row_groups, row_group;  // in groups of row_group tile rows (neighbouring rows share BVH nodes)
     double scale;                  // fixed-point units per 1.0 of the pixel accumulators (a power of two)
     int full_frame;                // 0: out holds the packed rows of the partition; 1: the whole frame
     double* out;                   // 3 doubles per pixel (may be peer-mapped memory of another GPU)

@@ -340,7 +340,8 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
 }
 
 static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
-                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats, bool full_frame = false) {
+                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats, bool full_frame = false,
+                         bool spread_rows = false) {
     if (!s || !cam) return fail(RTC_ERR_INVALID, "render: NULL scene or camera");
     if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
     if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
@@ -362,7 +363,42 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.n_parts = part->n_parts;
     P.rows = rtc_partition_rows(cam->vsize, part);
     P.tiles_x = (unsigned)((cam->hsize + RTC_TILE_W - 1) / RTC_TILE_W);
-    P.n_items = (unsigned long long)P.tiles_x * ((P.rows + RTC_TILE_H - 1) / RTC_TILE_H) * 32ull;
+    const unsigned n_tile_rows = (unsigned)((P.rows + RTC_TILE_H - 1) / RTC_TILE_H);
+    P.n_items = (unsigned long long)P.tiles_x * n_tile_rows * 32ull;
+    {
+        // Order of the tile rows.  Frame in device memory: top to bottom (neighbouring rows share BVH nodes and
+        // texels).  Frame in mapped host memory: groups of rows in golden-ratio stride order, so that pixels are
+        // produced at an even rate whatever the picture shows (RenderParams::row_stride).
+        static const long forced = [] {
+            const char* e = std::getenv("RTC_ROW_STRIDE");
+            return e ? std::atol(e) : -1L;
+        }();
+        static const long group = [] {
+            const char* e = std::getenv("RTC_ROW_GROUP");
+            return e ? std::atol(e) : 4L;
+        }();
+        P.row_group = (unsigned)(group > 0 ? group : 1);
+        P.n_row_groups = n_tile_rows / P.row_group;
+        unsigned st = 1;
+        if (forced >= 0 ? forced != 1 : spread_rows) {
+            st = forced > 1 ? (unsigned)forced : (unsigned)(0.381966 * P.n_row_groups);
+            auto gcd = [](unsigned a, unsigned b) {
+                while (b) {
+                    unsigned t = a % b;
+                    a = b;
+                    b = t;
+                }
+                return a;
+            };
+            while (st > 1 && gcd(st, P.n_row_groups) != 1) st--;
+            if (st == 0) st = 1;
+        }
+        P.row_stride = P.n_row_groups > 1 ? st % P.n_row_groups : 1;
+        if (P.row_stride == 0 || P.n_row_groups == 0) {
+            P.row_stride = 1;
+            P.n_row_groups = 0;
+        }
+    }
     P.full_frame = full_frame ? 1 : 0;
     P.scale = s->wf_scale;
     P.out = d_rgb;
@@ -504,7 +540,7 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
     // Canvas in pinned memory (rtc_host_alloc): the kernel stores every finished pixel straight into it
     // across PCIe, overlapped with the rendering of the others -- no staging frame, no copy afterwards.
     if (double* mapped = mapped_device_pointer(rgb_out))
-        return render_common(s, cam, max_depth, part, mapped, nullptr, 0, stats, true);
+        return render_common(s, cam, max_depth, part, mapped, nullptr, 0, stats, true, true);
     uint64_t rows = rtc_partition_rows(cam->vsize, part);
     int rc = ensure_frame(s, (size_t)rows * cam->hsize * 3 * sizeof(double) + 16);
     if (rc) return rc;
