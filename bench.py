@@ -268,12 +268,32 @@ def main():
     host = pkg.pinned_empty((HEIGHT, WIDTH, 3))
     host_pageable = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
 
-    pinned = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64).pin_memory() if (world > 1 and rank == 0) else None
+    # N > 1: the host canvas is ONE shared-memory segment that every rank maps and page-locks; each rank's public
+    # Camera.render(world, partition) stores its rows into it over its own PCIe link (multi_gpu.SharedHostFrame).
+    # Fallback (registration refused): assemble on rank 0's GPU as in step_device, then one copy to pinned memory.
+    shared = pinned = None
+    if world > 1:
+        ok = torch.zeros(1, device=dev)
+        try:
+            shared = mg.SharedHostFrame(WIDTH, HEIGHT, rank, world)
+        except Exception as e:  # noqa: BLE001
+            ok += 1
+            print("bench: shared host canvas unavailable on rank %d (%s)" % (rank, e), file=sys.stderr)
+        dist.all_reduce(ok)
+        if float(ok) > 0:
+            if shared is not None:
+                shared.close()
+            shared = None
+            pinned = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
 
     def step_e2e(canvas=None):
         if world == 1:  # the public call: Camera.render(world) -> host Canvas
             return camera.render(wld, DEPTH, None, out=host if canvas is None else canvas).stats
-        st = step_device()  # N > 1: render + NCCL gather, then the assembled frame goes to the host on rank 0
+        if shared is not None:  # the same public call on every rank, rows of its partition, then a barrier
+            st = camera.render(wld, DEPTH, part, out=shared.array).stats
+            dist.barrier()
+            return st
+        st = step_device()  # render + exchange on the GPUs, then the assembled frame goes to the host on rank 0
         if rank == 0:
             pinned.copy_(frame_on_rank0(), non_blocking=False)
         return st
@@ -325,6 +345,12 @@ def main():
         barrier()
         p_secs = time.perf_counter() - p0
         assert np.array_equal(host, host_pageable), "pinned and pageable canvases differ"
+    if shared is not None:
+        step_device()
+        barrier()
+        if rank == 0:  # the host canvas written by N ranks over N links == the frame assembled on rank 0's GPU
+            assert np.array_equal(shared.array, frame_on_rank0().cpu().numpy()), "shared host canvas differs from the device frame"
+        barrier()
     sampler.stop_flag = True
     sampler.join()
     # what the e2e leg is bounded by: a plain DMA copy of one frame, device -> page-locked host memory
@@ -350,6 +376,8 @@ def main():
     dev_ms, e_secs = float(t[0]), float(t[1])
     rays_all, e_rays_all, launches_all = float(tot[0]), float(tot[1]), int(tot[2])
 
+    if shared is not None:
+        shared.close()
     if rank == 0:
         peak, which = peaks()
         value = rays_all / (dev_ms * 1e-3) / 1e6
@@ -363,11 +391,15 @@ def main():
             "e2e": {"value": e_rays_all / e_secs / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * e_secs / args.steps,
                     "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24),
                     "canvas": "page-locked host memory (rtc_host_alloc): the kernel stores finished pixels into it over "
-                              "PCIe while rendering" if world == 1 else "rank 0 copies the assembled frame to pinned memory",
+                              "PCIe while rendering" if world == 1 else (
+                                  "one shared-memory host canvas, page-locked in every rank (cudaHostRegister): each rank's "
+                                  "Camera.render(world, partition) stores its rows into it over its own PCIe link, then a barrier"
+                                  if shared is not None else "rank 0 copies the assembled frame to pinned memory"),
                     "pageable_canvas_ms_per_step": (1e3 * p_secs / args.steps) if p_secs else None,
                     "d2h_copy_floor_ms": d2h_ms,
-                    "d2h_copy_floor": "one cudaMemcpy of the f64 frame (49.8 MB) into pinned memory on this box: the e2e step "
-                                      "cannot be shorter than max(kernel, this)"},
+                    "d2h_copy_floor": "one cudaMemcpy of the f64 frame (49.8 MB) into pinned memory over ONE link of this box"
+                                      + (": the e2e step cannot be shorter than max(kernel, this)" if world == 1 else
+                                         "; with the shared host canvas each of the N ranks moves 1/N of it over its own link")},
             "gpu_launches": launches_all,
             "rays_per_frame": rays_all / args.steps,
             # shadow rays the reference casts (and `value` counts) but this renderer does not trace because the

@@ -72,3 +72,52 @@ class PeerFrame:
         into the frame have been issued and completed."""
         self.handle.barrier()
         return self.frame
+
+
+class SharedHostFrame:
+    """The caller's HOST canvas shared by all ranks of the box: one POSIX shared-memory segment, mapped by every
+    process and (on GPUs) page-locked + device-mapped with cudaHostRegister.  Each rank then calls the public
+    Camera.render(world, partition=..., out=frame.array): rtc_render recognises the mapped memory and its kernel
+    stores the rank's rows straight into the host frame over that GPU's OWN PCIe link.  No assembly on rank 0,
+    no device->host copy of the whole frame through one link: the end-to-end exchange is a barrier."""
+
+    def __init__(self, width, height, rank, world, register=True, group=None):
+        import numpy as np
+        from multiprocessing import shared_memory
+        self.rank, self.world = rank, world
+        nbytes = height * width * 3 * 8
+        name = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            name[0] = self.shm.name
+        if world > 1:
+            dist.broadcast_object_list(name, src=0, group=group)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=name[0])
+            try:  # the segment belongs to rank 0: keep this process's resource tracker from unlinking it at exit
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:  # noqa: BLE001
+                pass
+        self.array = np.ndarray((height, width, 3), dtype=np.float64, buffer=self.shm.buf)
+        if rank == 0:
+            self.array[:] = 0.0
+        self.registered = False
+        if register:
+            rt = torch.cuda.cudart()
+            # cudaHostRegisterPortable (1) | cudaHostRegisterMapped (2)
+            err = rt.cudaHostRegister(self.array.ctypes.data, nbytes, 3)
+            if int(err) != 0:
+                raise RuntimeError("cudaHostRegister failed: %s" % err)
+            self.registered = True
+        if world > 1:
+            dist.barrier(group=group)
+
+    def close(self):
+        if self.registered:
+            torch.cuda.cudart().cudaHostUnregister(self.array.ctypes.data)
+            self.registered = False
+        self.array = None
+        self.shm.close()
+        if self.rank == 0:
+            self.shm.unlink()

@@ -64,3 +64,32 @@ def test_partition_rows_matches_c_abi():
                 assert len(ys) == c.partition_rows((8, r, n))
                 seen += ys
             assert sorted(seen) == list(range(vsize))  # a partition: every row exactly once
+
+
+def _shared_worker(rank, world, port, width, height, tile_rows, out_path):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
+        f = mg.SharedHostFrame(width, height, rank, world, register=False)  # no GPU here: the mapping logic only
+        for y in mg.partition_rows(height, tile_rows, rank, world):  # stand-in for the render of this rank's rows
+            f.array[y, :, 0] = y + 1
+            f.array[y, :, 1] = rank
+        dist.barrier()
+        if rank == 0:
+            torch.save(torch.from_numpy(f.array.copy()), out_path)
+        dist.barrier()
+        f.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shared_host_frame_world2_gloo(tmp_path):
+    """Two processes write their interleaved rows into ONE host canvas (the N-GPU end-to-end path of bench.py)."""
+    world, width, height, tile_rows = 2, 9, 21, 4
+    out = str(tmp_path / "frame.pt")
+    mp.spawn(_shared_worker, args=(world, _free_port(), width, height, tile_rows, out), nprocs=world, join=True)
+    frame = torch.load(out)
+    for y in range(height):
+        assert torch.all(frame[y, :, 0] == y + 1)
+        assert torch.all(frame[y, :, 1] == (y // tile_rows) % world)
