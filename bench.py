@@ -303,7 +303,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 4)):  # >= 4: the library measures its two kernels on the first four frames
+    for _ in range(max(args.warmup, 6)):  # >= 6: the library measures its kernel candidates on the first four to six frames
         step_device()
     barrier()
     sampler = ClockSampler(local_rank)

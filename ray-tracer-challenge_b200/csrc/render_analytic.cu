@@ -4,15 +4,20 @@
 
 namespace rtc {
 
-int launch_render_analytic(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream) {
-    render_kernel<false><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream) {
+    if (lpp == 4) render_kernel<false, 4><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+    else if (lpp == 2) render_kernel<false, 2><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+    else render_kernel<false, 1><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
     return (int)cudaGetLastError();
 }
 
 int occupancy_render_analytic(int* blocks_per_sm, size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(render_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(render_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(render_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(render_kernel<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel<false>, RTC_BLOCK, smem);
+    // the three instantiations share their launch bounds; the grid is sized by the one-lane-per-pixel kernel
+    return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel<false, 1>, RTC_BLOCK, smem);
 }
 
 int launch_wave_analytic(const DScene& S, const WaveParams& W, int grid, size_t smem, cudaStream_t stream) {

@@ -85,13 +85,24 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 #ifndef RTC_MIN_BLOCKS_MESH
 #define RTC_MIN_BLOCKS_MESH 4
 #endif
-template <bool MESH>
+// LPP = lanes per pixel (1, 2 or 4; rtc_api.cu picks it per partition size).  With LPP > 1 the LPP neighbouring lanes
+// of a warp take the SAME pixel: they trace the same closest-hit (and containers) queries side by side -- same ray, same
+// nodes, same result, same stack of child rays -- and share the LIGHTS of every hit, lane `sub` tracing the shadow rays
+// to lights sub, sub + LPP, ...  Each lane adds its lights' terms to its own fixed-point accumulator; the LPP partial
+// sums are added (integers: exact, the frame stays bit-identical) when the warp's lanes are all through.  The chain of
+// dependent trips behind a pixel shrinks from 1 + n_lights per hit to 1 + ceil(n_lights / LPP), at the price of LPP
+// times the closest-hit work: a loss while there are enough pixels to fill the machine, a gain for the small
+// partitions of a multi-GPU frame, whose time is the chain of their most expensive tile (profiles/README.md).
+template <bool MESH, int LPP>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
+    static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
     double* pk = s_mem + threadIdx.x;
     int* stack = reinterpret_cast<int*>(s_mem + PK_SLOTS * RTC_BLOCK) + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned sub = lane & (unsigned)(LPP - 1);  // which of the pixel's lanes this is
+    bool wpend = false;                                // LPP > 1: the pixel is through, its sum not yet written
 
     int state = ST_IDLE;
     bool done = false;
@@ -116,6 +127,32 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     q.c_leaf = -1;
     q.flag = 0;
     for (;;) {
+        if constexpr (LPP > 1) {
+            // every lane of the warp is through with its pixel: add up the partial sums of the lanes that shared one
+            if (__all_sync(0xffffffffu, state == ST_IDLE)) {
+                long long a0 = __double_as_longlong(PK(PK_PCOL)), a1 = __double_as_longlong(PK(PK_PCOL + 1)),
+                          a2 = __double_as_longlong(PK(PK_PCOL + 2));
+#pragma unroll
+                for (int sft = 1; sft < LPP; sft <<= 1) {
+                    a0 += __shfl_xor_sync(0xffffffffu, a0, sft);
+                    a1 += __shfl_xor_sync(0xffffffffu, a1, sft);
+                    a2 += __shfl_xor_sync(0xffffffffu, a2, sft);
+                }
+                if (wpend && sub == 0) {
+                    const double inv_scale = 1.0 / P.scale;  // a power of two: exact
+                    V3 pcol = v3((double)a0 * inv_scale, (double)a1 * inv_scale, (double)a2 * inv_scale);
+                    if (P.out8) {
+                        reinterpret_cast<uchar4*>(P.out8)[pix] = make_uchar4(quantise(pcol.x), quantise(pcol.y), quantise(pcol.z), 255);
+                    } else {
+                        double* o = P.out + pix * 3;
+                        o[0] = pcol.x;
+                        o[1] = pcol.y;
+                        o[2] = pcol.z;
+                    }
+                }
+                wpend = false;
+            }
+        }
         // ---- refill idle lanes ------------------------------------------------------------------
         unsigned need = __ballot_sync(0xffffffffu, state == ST_IDLE && !done);
 #if RTC_REFILL_MIN > 1
@@ -133,8 +170,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     done = true;
                 } else {
                     // 8x4 pixel tiles, row-major tiles over the packed rows of this partition
-                    unsigned long long tile = item >> 5;
-                    unsigned in = (unsigned)(item & 31u);
+                    const unsigned long long pitem = item / (unsigned)LPP;  // the LPP lanes of a pixel hold consecutive items
+                    unsigned long long tile = pitem >> 5;
+                    unsigned in = (unsigned)(pitem & 31u);
                     unsigned long long px = (tile % P.tiles_x) * RTC_TILE_W + (in & (RTC_TILE_W - 1u));
                     unsigned long long trow = tile / P.tiles_x;
                     if (P.row_stride != 1) {  // strided order of the row groups (render_params.h), 32-bit arithmetic
@@ -162,7 +200,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         pk_st(pk, PK_PCOL, v3(0, 0, 0));  // +0.0 is also the bit pattern of int64 0
                         rsp = 0;
                         state = ST_CLOSEST;
-                        n_primary++;
+                        if (sub == 0) n_primary++;
                     }
                     // items outside the frame are simply dropped: the lane asks again next trip
                 }
@@ -274,7 +312,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
                 pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
-                h_light = 0;
+                h_light = (int)sub;
                 PK(PK_N1) = 1.0;
                 PK(PK_N2) = 1.0;
                 // n1/n2 only reach a result through refractedColor / schlick, both gated on
@@ -282,7 +320,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 // ... and when every material of the scene has refractive index 1.0 (dragons.json's glass boxes),
                 // n1 = n2 = 1.0 whatever the containers list holds (world.zig:236-254): the walk is skipped.
                 if (M.transparency != 0.0 && !S.ri_all_one) state = ST_CONTAINERS;
-                else state = S.n_lights > 0 ? ST_SHADOW : -1;  // no lights: straight to the children below
+                else state = S.n_lights > (int)sub ? ST_SHADOW : -1;  // no lights (left for this lane): straight to the children below
             }
         } else if (state == ST_CONTAINERS) {
             double ri_hit = S.materials[S.leaves[hit_leaf].material].refractive_index;
@@ -295,7 +333,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_N1) = ri_c;
                 PK(PK_N2) = ri_hit;
             }
-            state = S.n_lights > 0 ? ST_SHADOW : -1;
+            state = S.n_lights > (int)sub ? ST_SHADOW : -1;
         } else if (state == ST_SHADOW) {
             // Material.lighting (material.zig:40-74)
             const rtc_light& Lg = S.lights[h_light];
@@ -331,7 +369,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     PK(PK_PCOL + k) = __longlong_as_double(a);
                 }
             }
-            h_light++;
+            h_light += LPP;
             if (h_light >= S.n_lights) state = -1;
         }
 
@@ -382,7 +420,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     if (rsp < RTC_RAY_STACK) {
                         rays[rsp++] = {under.x, under.y, under.z, refr_dir.x, refr_dir.y, refr_dir.z, rw * refr_w, remaining - 1, 0};
                     }
-                    n_secondary++;
+                    if (sub == 0) n_secondary++;
                 }
                 if (spawn_refl) {
                     V3 h_over = h_point + h_normal * 1e-5;
@@ -390,7 +428,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     if (rsp < RTC_RAY_STACK) {
                         rays[rsp++] = {h_over.x, h_over.y, h_over.z, reflectv.x, reflectv.y, reflectv.z, rw * refl_w, remaining - 1, 0};
                     }
-                    n_secondary++;
+                    if (sub == 0) n_secondary++;
                 }
             }
             pop_next = true;
@@ -404,6 +442,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_RW) = tk.w;
                 remaining = tk.remaining;
                 state = ST_CLOSEST;
+            } else if (LPP > 1) {
+                wpend = true;  // written at the top of the loop, once the lanes sharing this pixel are all through
+                state = ST_IDLE;
             } else {
                 const double inv_scale = 1.0 / P.scale;  // a power of two: exact
                 V3 pcol = v3((double)__double_as_longlong(PK(PK_PCOL)) * inv_scale,

@@ -32,7 +32,7 @@ struct RenderParams {
     int max_depth;
     unsigned int tile_rows, part, n_parts;
     unsigned long long rows;       // rows of this partition
-    unsigned long long n_items;    // tiles_x * tiles_y * 32 work items (some fall outside the frame)
+    unsigned long long n_items;    // tiles_x * tiles_y * 32 pixels (some fall outside the frame) x lanes per pixel
     unsigned int tiles_x;
     // Groups of tile rows are handed out in the order (k * row_stride) % n_row_groups, k = 0, 1, ... (row_stride coprime
     // to n_row_groups, about 0.38 of it; the rows past the last full group keep their place): consecutive work is spread over the frame, so cheap and expensive regions of
@@ -113,8 +113,9 @@ int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 
 // render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
 // smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).
-int launch_render_mesh(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream);
-int launch_render_analytic(const DScene& S, const RenderParams& P, int grid, size_t smem, cudaStream_t stream);
+// lpp = lanes per pixel (1, 2 or 4): render_kernel<MESH, LPP>; P.n_items counts lanes, i.e. pixels x lpp.
+int launch_render_mesh(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
+int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
 int occupancy_render_mesh(int* blocks_per_sm, size_t smem);
 int occupancy_render_analytic(int* blocks_per_sm, size_t smem);
 

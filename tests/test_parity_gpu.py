@@ -176,6 +176,55 @@ def test_megakernel_and_wavefront_are_bit_identical(pkg, name):
         assert out["mega"][1][key] == out["wave"][1][key]
 
 
+@pytest.mark.parametrize("name", ["smoke", "cover", "dragons", "groups", "align_check"])
+def test_lanes_per_pixel_are_bit_identical(pkg, name):
+    """render_kernel<MESH, LPP>: 2 or 4 lanes of a warp share a pixel and split its lights; the partial sums are
+    integers, so whole frames, partitions, RGBA8 frames and ray counts equal the one-lane-per-pixel kernel's bit
+    for bit (the library may use it for small partitions without changing a pixel)."""
+    from tests.golden import make_golden
+    if name == "smoke":
+        text, assets, (w, h) = scenes.SMOKE_SCENE, "", (163, 97)  # ragged: not a multiple of the 8x4 tile
+    else:
+        s = scenes.shipped_scene(name)
+        if s is None:
+            pytest.skip("reference assets not staged")
+        text, assets = s
+        w, h = make_golden.SIZES[name]
+        w, h = 2 * w, 2 * h
+    info = pkg.parse_scene(text, assets, w, h)
+    out = {}
+    try:
+        os.environ["RTC_KERNEL"] = "mega"
+        for lpp in (1, 2, 4):
+            os.environ["RTC_LPP"] = str(lpp)
+            c = info.camera.render(info.world)
+            p = info.camera.render(info.world, partition=(8, 1, 3))
+            r8, _ = info.camera.render_rgba8(info.world)
+            out[lpp] = (c.pixels.copy(), p.pixels.copy(), r8.copy(), c.stats.as_dict())
+    finally:
+        os.environ.pop("RTC_KERNEL", None)
+        os.environ.pop("RTC_LPP", None)
+    assert out[1][0].any()
+    for lpp in (2, 4):
+        for k in range(3):
+            assert np.array_equal(out[1][k], out[lpp][k])
+        for key in ("primary", "shadow", "secondary", "shadow_culled"):
+            assert out[1][3][key] == out[lpp][3][key]
+
+
+def test_small_partitions_measure_two_lanes_per_pixel(pkg):
+    """A partition that leaves the machine underfilled renders frames 5-6 with two lanes per pixel (third candidate
+    of the library's first-frames measurement): every frame of the sequence is the same frame."""
+    s = scenes.shipped_scene("dragons")
+    if s is None:
+        pytest.skip("reference assets not staged")
+    info = pkg.parse_scene(s[0], s[1], 640, 360)
+    frames = [info.camera.render(info.world, partition=(8, 2, 4)).pixels.copy() for _ in range(8)]
+    assert frames[0].any()
+    for f in frames[1:]:
+        assert np.array_equal(frames[0], f)
+
+
 def test_errors(pkg):
     with pytest.raises(pkg.RtcError):
         pkg.World(b"\0" * 512)

@@ -36,7 +36,7 @@ def main():
         per = []
         for r in range(min(n, 8)):
             best = 1e9
-            for _ in range(8):
+            for _ in range(10):
                 if not a.no_flush:
                     flush.zero_()
                 torch.cuda.synchronize()
