@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
 
     int state = ST_IDLE;
     bool done = false;
+    PK(PK_SPARE) = -1.0;  // lane 0: tile in flight (none)
     int err = 0;
     unsigned n_primary = 0, n_shadow = 0, n_secondary = 0, n_culled = 0;  // per thread: far below 2^32
 
@@ -160,6 +161,16 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
         if (__popc(need) < RTC_REFILL_MIN && __any_sync(0xffffffffu, state != ST_IDLE)) need = 0;
 #endif
         if (need) {
+            // cost of the tile this warp is through with (clock ticks / 64), for the order of the NEXT frame
+            if (P.tile_cost && lane == 0 && PK(PK_SPARE) >= 0.0) {
+                const long long t0 = __double_as_longlong(PK(PK_SPARE + 1));
+                const unsigned cost = (unsigned)((clock64() - t0) >> 6);
+                atomicAdd(P.tile_cost + (unsigned)PK(PK_SPARE), cost);
+#ifndef RTC_TRIP_PROBE
+                atomicAdd(P.counters + 6, (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
+#endif
+                PK(PK_SPARE) = -1.0;
+            }
             unsigned long long base = 0;
             int leader = __ffs(need) - 1;
             if ((int)lane == leader) base = atomicAdd(P.counters, (unsigned long long)__popc(need));
@@ -173,6 +184,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     const unsigned long long pitem = item / (unsigned)LPP;  // the LPP lanes of a pixel hold consecutive items
                     unsigned long long tile = pitem >> 5;
                     unsigned in = (unsigned)(pitem & 31u);
+                    if (P.tile_order) tile = __ldg(P.tile_order + tile);  // most expensive tiles of the last frame first
+                    if (P.tile_cost && lane == 0) {
+                        PK(PK_SPARE) = (double)tile;
+                        PK(PK_SPARE + 1) = __longlong_as_double(clock64());
+                    }
                     unsigned long long px = (tile % P.tiles_x) * RTC_TILE_W + (in & (RTC_TILE_W - 1u));
                     unsigned long long trow = tile / P.tiles_x;
                     if (P.row_stride != 1) {  // strided order of the row groups (render_params.h), 32-bit arithmetic

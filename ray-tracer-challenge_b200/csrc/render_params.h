@@ -43,7 +43,12 @@ struct RenderParams {
     int full_frame;                // 0: out holds the packed rows of the partition; 1: the whole frame
     double* out;                   // 3 doubles per pixel (may be peer-mapped memory of another GPU)
     unsigned char* out8;           // or RGBA8 (NULL when `out` is used)
-    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
+    // Tiles are handed out in the order tile_order[0], tile_order[1], ... (NULL: 0, 1, ...): a permutation of the tiles
+    // of this partition, the most expensive ones of the previous frame first (rtc_api.cu).  tile_cost[tile] receives
+    // the time the warps spent on the tile in this frame (NULL: not recorded).
+    const unsigned int* tile_order;
+    unsigned int* tile_cost;
+    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays, [6] sum of tile_cost
 };
 
 // ---- wavefront path (render_wavefront.cuh) ------------------------------------------------------------
@@ -110,6 +115,9 @@ int launch_wave_analytic(const DScene& S, const WaveParams& W, int grid, size_t 
 int occupancy_wave_mesh(int* blocks_per_sm, size_t smem);
 int occupancy_wave_analytic(int* blocks_per_sm, size_t smem);
 int launch_resolve(const ResolveParams& R, cudaStream_t stream);
+// tile_order.cu: order[] = the tiles 0..n_tiles-1, stably sorted into four cost buckets (most expensive first)
+int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
+                      cudaStream_t stream);
 
 // render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
 // smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).

@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -59,6 +60,11 @@ struct rtc_scene {
     // lanes_per_pixel); per pixel-count of the last frame
     float best_ms[3] = {-1.0f, -1.0f, -1.0f};
     size_t tuned_pixels = 0;
+    // tile order of the megakernel: cost of every tile in the last frame, and the permutation made from it
+    unsigned* d_tile_cost = nullptr;
+    unsigned* d_tile_order = nullptr;
+    size_t tile_cap = 0;      // tiles the two arrays hold
+    size_t order_tiles = 0;   // tiles the current permutation covers (0: none yet)
 };
 
 // RTC_KERNEL=mega|wave pins the kernel; default (auto) measures both on the first four frames of a scene.
@@ -124,6 +130,8 @@ void rtc_scene_destroy(rtc_scene* s) {
     cudaSetDevice(s->device);
     if (s->slab) cudaFree(s->slab);
     if (s->d_counters) cudaFree(s->d_counters);
+    if (s->d_tile_cost) cudaFree(s->d_tile_cost);
+    if (s->d_tile_order) cudaFree(s->d_tile_order);
     for (int i = 0; i < 2; i++) {
         if (s->wf_rays[i]) cudaFree(s->wf_rays[i]);
         if (s->wf_hits[i]) cudaFree(s->wf_hits[i]);
@@ -432,6 +440,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         s->tuned_pixels = n_px;
         s->frames = 0;
         s->best_ms[0] = s->best_ms[1] = s->best_ms[2] = -1.0f;
+        s->order_tiles = 0;
     }
     int which = forced_kernel();
     if (which < 0) {
@@ -461,6 +470,31 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         }
         s->best_ms[1] = 1e30f;  // queue overflow: this scene stays with the megakernel; redo the frame below
     }
+    const size_t n_tiles = (size_t)(P.n_items / 32);
+    // Tiles in the order of their cost in the previous frame of this size (tile_order.cu); RTC_LPT=0 keeps the plain order.
+    // Not for canvases in mapped host memory: there the time a warp spends on a tile is mostly the back-pressure of its
+    // stores on the PCIe link, and the even byte rate of the strided order matters more (measured: e2e 1.49 -> 1.91 ms).
+    static const int lpt_env = [] {
+        const char* e = std::getenv("RTC_LPT");
+        return e ? std::atoi(e) : 1;
+    }();
+    const bool lpt = lpt_env == 2 || (lpt_env == 1 && !spread_rows);
+    if (lpt) {
+        if (s->tile_cap < n_tiles) {
+            if (s->d_tile_cost) cudaFree(s->d_tile_cost);
+            if (s->d_tile_order) cudaFree(s->d_tile_order);
+            s->d_tile_cost = s->d_tile_order = nullptr;
+            s->tile_cap = 0;
+            // costs, then the scratch counts of tile_order.cu (4 per 1024 tiles)
+            CUDA_TRY(cudaMalloc(&s->d_tile_cost, (n_tiles + 4 * (n_tiles / 1024 + 1)) * sizeof(unsigned)));
+            CUDA_TRY(cudaMalloc(&s->d_tile_order, n_tiles * sizeof(unsigned)));
+            s->tile_cap = n_tiles;
+            s->order_tiles = 0;
+        }
+        CUDA_TRY(cudaMemsetAsync(s->d_tile_cost, 0, n_tiles * sizeof(unsigned), stream));
+        P.tile_cost = s->d_tile_cost;
+        P.tile_order = s->order_tiles == n_tiles ? s->d_tile_order : nullptr;
+    }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
     P.n_items *= (unsigned long long)lpp;
@@ -472,6 +506,11 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     CUDA_TRY(cudaStreamSynchronize(stream));
     float ms = 0;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    if (lpt) {  // the next frame's order; runs behind this call, ahead of the next frame on the same stream
+        CUDA_TRY((cudaError_t)launch_tile_order(s->d_tile_cost, s->d_counters + 6, s->d_tile_cost + n_tiles, s->d_tile_order,
+                                                (unsigned)n_tiles, stream));
+        s->order_tiles = n_tiles;
+    }
 #ifdef RTC_TRIP_PROBE
     std::fprintf(stderr, "trip probe: max trip %.1f us, trips %llu, > 50 us: %llu, > 20 us: %llu (kernel %.3f ms)\n", c[6] / 1965.0,
                  c[7] & 0xffffffffull, (c[7] >> 32) & 0xffffull, c[7] >> 48, ms);
@@ -482,7 +521,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         stats->secondary_rays = c[3];
         stats->pixels = P.rows * cam->hsize;
         stats->kernel_ms = ms;
-        stats->launches = 1;
+        stats->launches = lpt ? 3 : 1;  // render_kernel (+ the two kernels of tile_order.cu)
         stats->shadow_rays_culled = c[5];
     }
     if (s->best_ms[slot] < 0.0f || ms < s->best_ms[slot]) s->best_ms[slot] = ms;

@@ -1,0 +1,108 @@
+// Order in which the megakernel hands out the tiles of the NEXT frame, made on the device from the time its warps
+// spent on every tile of THIS frame (RenderParams::tile_cost / tile_order, render_kernel.cuh).
+//
+// Why: the tiles of a frame differ in cost by more than an order of magnitude (dragons.json 1920x1080: mean 38 us of
+// warp time per 8x4 tile, 1 % of the tiles above 300 us, the longest 600 us -- pixels whose ray trees run through the
+// glass boxes), and a persistent grid that meets such a tile late finishes late: the tail behind an empty work queue
+// was a quarter of the frame.  Longest-processing-time-first scheduling needs the costs in advance; the previous frame
+// of the same scene and frame size is a good predictor (re-renders of the bench, orbiting cameras of lib.zig:166-190).
+// Nothing is cached or skipped: every pixel is traced in every frame, only the ORDER of the work changes, and the
+// frame does not depend on it (each pixel is accumulated by itself in exact integers).
+//
+// The order is a STABLE sort into four buckets -- cost >= 8x, 4x, 2x the mean, the rest -- so that tiles of like cost
+// keep the order they had (top to bottom, or the strided order of a mapped canvas): neighbouring tiles stay neighbours
+// in time, which a full sort by cost loses (measured: teapot.json 0.61 -> 0.66 ms with a full sort).
+//
+// Two small launches behind the render kernel (a single CTA doing all of it took 0.14 ms for the 64,800 tiles of a
+// 1080p frame, latency-bound): bucket counts per block of 1024 consecutive tiles, then every block scans the counts of
+// the blocks before it (a few hundred numbers) and scatters its tiles, ranked by ballot so that the order inside a
+// bucket is the tile order.  The mean comes from the render kernel (counters[6] = sum of all tile costs).
+#include <cuda_runtime.h>
+
+#include "render_params.h"
+
+namespace rtc {
+
+namespace {
+constexpr int T = 1024;
+
+__device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum) {
+    const unsigned long long c = (unsigned long long)cost * n;  // cost / mean = c / sum; cost < 2^32, n < 2^24
+    return c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+}
+
+// counts[b * gridDim.x + block] = tiles of bucket b among the block's 1024
+__global__ void __launch_bounds__(T) tile_count_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
+                                                       unsigned* __restrict__ counts, unsigned n) {
+    __shared__ unsigned s_cnt[4];
+    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const unsigned i = blockIdx.x * T + threadIdx.x;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const unsigned m = __ballot_sync(0xffffffffu, b == k);
+        if ((threadIdx.x & 31u) == 0 && m) atomicAdd(&s_cnt[k], __popc(m));
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) counts[threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
+                                                         const unsigned* __restrict__ counts, unsigned* __restrict__ order, unsigned n) {
+    __shared__ unsigned s_base[4];           // where this block's tiles of bucket b start
+    __shared__ unsigned s_warp[4][T / 32];   // tiles of bucket b in each warp, then their exclusive prefix
+    __shared__ unsigned s_red[T / 32];
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    // flattened (bucket, block) index of this block's bucket b is b * gridDim.x + blockIdx.x: sum everything before it
+    const unsigned total = 4 * gridDim.x;
+    for (int b = 0; b < 4; b++) {
+        const unsigned end = b * gridDim.x + blockIdx.x;
+        unsigned part = 0;
+        for (unsigned j = tid; j < end; j += T) part += counts[j];
+        for (int s = 16; s > 0; s >>= 1) part += __shfl_down_sync(0xffffffffu, part, s);
+        if (lane == 0) s_red[warp] = part;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned t = 0;
+            for (int w = 0; w < T / 32; w++) t += s_red[w];
+            s_base[b] = t;
+        }
+        __syncthreads();
+    }
+    (void)total;
+    const unsigned i = blockIdx.x * T + tid;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
+    unsigned rank = 0;  // among the tiles of my bucket in my warp
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const unsigned m = __ballot_sync(0xffffffffu, b == k);
+        if (b == k) rank = __popc(m & ((1u << lane) - 1u));
+        if (lane == 0) s_warp[k][warp] = __popc(m);
+    }
+    __syncthreads();
+    if (warp < 4) {  // warp k: exclusive prefix over the 32 warp counts of bucket k
+        const unsigned c = s_warp[warp][lane];
+        unsigned incl = c;
+        for (int s = 1; s < 32; s <<= 1) {
+            const unsigned up = __shfl_up_sync(0xffffffffu, incl, s);
+            if ((int)lane >= s) incl += up;
+        }
+        s_warp[warp][lane] = incl - c;
+    }
+    __syncthreads();
+    if (b >= 0) order[s_base[b] + s_warp[b][warp] + rank] = i;
+}
+}  // namespace
+
+// scratch: 4 * ceil(n_tiles / 1024) unsigned; sum: the render kernel's sum of all tile costs (device memory)
+int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
+                      cudaStream_t stream) {
+    if (!n_tiles) return 0;
+    const unsigned blocks = (n_tiles + T - 1) / T;
+    tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles);
+    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, n_tiles);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace rtc
