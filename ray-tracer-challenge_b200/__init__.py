@@ -42,11 +42,11 @@ class rtc_partition(ctypes.Structure):
 class rtc_stats(ctypes.Structure):
     _fields_ = [("primary_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64),
                 ("secondary_rays", ctypes.c_uint64), ("pixels", ctypes.c_uint64), ("kernel_ms", ctypes.c_float),
-                ("pad", ctypes.c_float), ("launches", ctypes.c_uint64), ("shadow_rays_culled", ctypes.c_uint64)]
+                ("kernel", ctypes.c_uint32), ("launches", ctypes.c_uint64), ("shadow_rays_culled", ctypes.c_uint64)]
 
     def as_dict(self):
         return {"primary": self.primary_rays, "shadow": self.shadow_rays, "secondary": self.secondary_rays,
-                "pixels": self.pixels, "kernel_ms": self.kernel_ms, "launches": self.launches,
+                "pixels": self.pixels, "kernel_ms": self.kernel_ms, "launches": self.launches, "kernel": self.kernel,
                 "shadow_culled": self.shadow_rays_culled}
 
     @property

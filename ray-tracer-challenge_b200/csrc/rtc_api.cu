@@ -355,6 +355,7 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
         stats->pixels = n_pixels;
         stats->kernel_ms = ms;
         stats->launches = (unsigned long long)n_launch + 1;  // + resolve
+        stats->kernel = 1u;
         stats->shadow_rays_culled = c[WC_CULLED];
     }
     if (c[WC_ERR]) {
@@ -473,7 +474,9 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     const size_t n_tiles = (size_t)(P.n_items / 32);
     // Tiles in the order of their cost in the previous frame of this size (tile_order.cu); RTC_LPT=0 keeps the plain order.
     // Not for canvases in mapped host memory: there the time a warp spends on a tile is mostly the back-pressure of its
-    // stores on the PCIe link, and the even byte rate of the strided order matters more (measured: e2e 1.49 -> 1.91 ms).
+    // stores on the PCIe link, and the even byte rate of the strided order matters more (measured: e2e 1.49 -> 1.91 ms;
+    // with the cost counted in trips of the render loop instead of clock ticks 1.80: it is the burst of cheap tiles at the
+    // end that costs, not the noise of the measurement).
     static const int lpt_env = [] {
         const char* e = std::getenv("RTC_LPT");
         return e ? std::atoi(e) : 1;
@@ -522,6 +525,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         stats->pixels = P.rows * cam->hsize;
         stats->kernel_ms = ms;
         stats->launches = lpt ? 3 : 1;  // render_kernel (+ the two kernels of tile_order.cu)
+        stats->kernel = lpp > 1 ? 2u : 0u;
         stats->shadow_rays_culled = c[5];
     }
     if (s->best_ms[slot] < 0.0f || ms < s->best_ms[slot]) s->best_ms[slot] = ms;
