@@ -46,7 +46,7 @@ typedef struct rtc_stats {
     uint64_t primary_rays, shadow_rays, secondary_rays; /* world.zig:91-92,160-165,178-187 */
     uint64_t pixels;
     float kernel_ms; /* CUDA-event time of the render kernel(s) of this call */
-    uint32_t kernel; /* which kernel rendered the frame: 0 megakernel, 1 wavefront, 2 megakernel with two lanes per pixel */
+    uint32_t kernel; /* which kernel rendered the frame: 0 megakernel, 1 wavefront, 2 megakernel with several lanes per pixel (small partitions) */
     uint64_t launches; /* kernels launched by this call */
     /* shadow rays (counted in shadow_rays, as the reference casts them) that were NOT traced because
      * the light is behind the surface: lighting() returns ambient either way (material.zig:55-63) */

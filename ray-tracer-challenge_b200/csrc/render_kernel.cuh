@@ -96,12 +96,20 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 template <bool MESH, int LPP>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
     static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");
+    // LPP == 0 ("mixed"): four lanes per pixel on the tiles the last frame found expensive (the first *P.heavy_tiles
+    // entries of tile_order: cost >= 8x the mean), one lane per pixel on all others.  The few per cent of the tiles
+    // whose chains of dependent trips set the time of a small partition get the short chain; the rest of the frame
+    // is not traced twice.
+    constexpr bool MIXED = LPP == 0;
+    const unsigned long long heavy_items = MIXED && P.tile_order ? (unsigned long long)__ldg(P.heavy_tiles) * 128ull : 0ull;
+    const unsigned long long n_items = P.n_items + heavy_items / 4 * 3;  // a heavy tile is 128 lane items instead of 32
+    int lpp = MIXED ? 1 : LPP;  // lanes per pixel of the tile this warp is working on
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
     double* pk = s_mem + threadIdx.x;
     int* stack = reinterpret_cast<int*>(s_mem + PK_SLOTS * RTC_BLOCK) + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned sub = lane & (unsigned)(LPP - 1);  // which of the pixel's lanes this is
+    unsigned sub = MIXED ? 0u : lane & (unsigned)(LPP - 1);  // which of the pixel's lanes this is
     bool wpend = false;                                // LPP > 1: the pixel is through, its sum not yet written
 
     int state = ST_IDLE;
@@ -128,13 +136,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     q.c_leaf = -1;
     q.flag = 0;
     for (;;) {
-        if constexpr (LPP > 1) {
+        if constexpr (LPP != 1) {
             // every lane of the warp is through with its pixel: add up the partial sums of the lanes that shared one
-            if (__all_sync(0xffffffffu, state == ST_IDLE)) {
+            if (__all_sync(0xffffffffu, state == ST_IDLE) && __any_sync(0xffffffffu, lpp > 1)) {
                 long long a0 = __double_as_longlong(PK(PK_PCOL)), a1 = __double_as_longlong(PK(PK_PCOL + 1)),
                           a2 = __double_as_longlong(PK(PK_PCOL + 2));
 #pragma unroll
-                for (int sft = 1; sft < LPP; sft <<= 1) {
+                for (int sft = 1; sft < (MIXED ? 4 : LPP); sft <<= 1) {
                     a0 += __shfl_xor_sync(0xffffffffu, a0, sft);
                     a1 += __shfl_xor_sync(0xffffffffu, a1, sft);
                     a2 += __shfl_xor_sync(0xffffffffu, a2, sft);
@@ -177,11 +185,19 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
             base = __shfl_sync(0xffffffffu, base, leader);
             if (state == ST_IDLE && !done) {
                 unsigned long long item = base + __popc(need & lt_mask);
-                if (item >= P.n_items) {
+                if (item >= n_items) {
                     done = true;
                 } else {
                     // 8x4 pixel tiles, row-major tiles over the packed rows of this partition
-                    const unsigned long long pitem = item / (unsigned)LPP;  // the LPP lanes of a pixel hold consecutive items
+                    unsigned long long pitem;  // the lanes of a pixel hold consecutive items
+                    if constexpr (MIXED) {
+                        const bool heavy = item < heavy_items;  // the same for the whole warp: heavy_items % 32 == 0
+                        lpp = heavy ? 4 : 1;
+                        sub = heavy ? (unsigned)item & 3u : 0u;
+                        pitem = heavy ? item >> 2 : item - heavy_items / 4 * 3;
+                    } else {
+                        pitem = item / (unsigned)LPP;
+                    }
                     unsigned long long tile = pitem >> 5;
                     unsigned in = (unsigned)(pitem & 31u);
                     if (P.tile_order) tile = __ldg(P.tile_order + tile);  // most expensive tiles of the last frame first
@@ -385,7 +401,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     PK(PK_PCOL + k) = __longlong_as_double(a);
                 }
             }
-            h_light += LPP;
+            h_light += lpp;
             if (h_light >= S.n_lights) state = -1;
         }
 
@@ -458,7 +474,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_RW) = tk.w;
                 remaining = tk.remaining;
                 state = ST_CLOSEST;
-            } else if (LPP > 1) {
+            } else if (LPP != 1 && lpp > 1) {
                 wpend = true;  // written at the top of the loop, once the lanes sharing this pixel are all through
                 state = ST_IDLE;
             } else {

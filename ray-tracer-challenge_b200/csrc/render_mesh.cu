@@ -5,7 +5,8 @@
 namespace rtc {
 
 int launch_render_mesh(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream) {
-    if (lpp == 4) render_kernel<true, 4><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+    if (lpp == 0) render_kernel<true, 0><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
+    else if (lpp == 4) render_kernel<true, 4><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
     else if (lpp == 2) render_kernel<true, 2><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
     else render_kernel<true, 1><<<grid, RTC_BLOCK, smem, stream>>>(S, P);
     return (int)cudaGetLastError();
@@ -15,6 +16,7 @@ int occupancy_render_mesh(int* blocks_per_sm, size_t smem) {
     cudaError_t e = cudaFuncSetAttribute(render_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(render_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(render_kernel<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(render_kernel<true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     // the three instantiations share their launch bounds; the grid is sized by the one-lane-per-pixel kernel
     return (int)cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, render_kernel<true, 1>, RTC_BLOCK, smem);

@@ -48,6 +48,7 @@ struct RenderParams {
     // the time the warps spent on the tile in this frame (NULL: not recorded).
     const unsigned int* tile_order;
     unsigned int* tile_cost;
+    const unsigned int* heavy_tiles;  // device word: how many leading entries of tile_order cost >= 8x the mean (LPP == 0)
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays, [6] sum of tile_cost
 };
 
@@ -121,7 +122,8 @@ int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsig
 
 // render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
 // smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).
-// lpp = lanes per pixel (1, 2 or 4): render_kernel<MESH, LPP>; P.n_items counts lanes, i.e. pixels x lpp.
+// lpp = lanes per pixel (1, 2 or 4; 0 = four on last frame's expensive tiles, one elsewhere): render_kernel<MESH, LPP>;
+// P.n_items counts lanes, i.e. pixels x lpp (lpp 0: pixels, the kernel adds the extra lanes of the expensive tiles).
 int launch_render_mesh(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
 int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
 int occupancy_render_mesh(int* blocks_per_sm, size_t smem);

@@ -56,8 +56,8 @@ struct rtc_scene {
     // wavefront wins where pixels have long or branching ray trees, the megakernel where they do not and on
     // small frames): frames 1-4 alternate between the heuristic choice and the other kernel, later frames use the faster one.
     int frames = 0;
-    // [0] megakernel, [1] wavefront, [2] megakernel with two lanes per pixel (small partitions only, see
-    // lanes_per_pixel); per pixel-count of the last frame
+    // [0] megakernel, [1] wavefront, [2] megakernel with four lanes per pixel on last frame's expensive tiles (small
+    // partitions only, see mixed_candidate); per pixel-count of the last frame
     float best_ms[3] = {-1.0f, -1.0f, -1.0f};
     size_t tuned_pixels = 0;
     // tile order of the megakernel: cost of every tile in the last frame, and the permutation made from it
@@ -81,16 +81,19 @@ static int forced_lpp(const rtc_scene* s) {
     const char* e = std::getenv("RTC_LPP");  // read at every render: tests switch it between frames
     if (!e) return -1;
     int lpp = std::atoi(e);
-    if (lpp != 1 && lpp != 2 && lpp != 4) return -1;
+    if (lpp != 0 && lpp != 1 && lpp != 2 && lpp != 4) return -1;
+    if (lpp == 0) return s->d.n_lights >= 2 ? 0 : 1;  // mixed: four lanes per pixel on last frame's expensive tiles
     while (lpp > 1 && s->d.n_lights < lpp) lpp >>= 1;  // lanes without a light would only repeat the closest-hit query
     return lpp;
 }
-// Two lanes per pixel are worth MEASURING (third candidate of the first-frames measurement below) where the frame time
-// is the chain of trips behind the most expensive tile rather than the machine's throughput: partitions that give a
-// resident warp fewer than 8 tiles (a 1/4 or 1/8 partition of a 1080p frame on a B200), in scenes with >= 2 lights.
-// Measured on dragons.json 1080p (kernel ms, 1 / 2 / 4 lanes): whole frame 1.23 / 1.73 / 2.41, 1/8 partition
-// 0.383 / 0.333 / 0.392 (profiles/README.md).
-static bool lpp2_candidate(const rtc_scene* s, size_t n_px) {
+// The mixed kernel (render_kernel<MESH, 0>: four lanes per pixel on the tiles that cost >= 8x the mean in the last
+// frame, one elsewhere) is worth MEASURING (third candidate of the first-frames measurement below) where the frame
+// time is the chain of trips behind the most expensive tile rather than the machine's throughput: partitions that
+// give a resident warp fewer than 8 tiles (a 1/4 or 1/8 partition of a 1080p frame on a B200), in scenes with >= 2
+// lights.  Measured on dragons.json 1080p, L2 flushed (kernel ms, one lane / two lanes / mixed): 1/4 partition
+// 0.46 / 0.45 / 0.36, 1/8 partition 0.48 / 0.39 / 0.33; 1/2 partition 0.58 / - / 0.63, whole frame 1.04 / 1.60 / 1.19
+// (profiles/README.md).
+static bool mixed_candidate(const rtc_scene* s, size_t n_px) {
     const size_t warps = (size_t)s->grid * (RTC_BLOCK_THREADS / 32);
     return s->d.n_lights >= 2 && n_px / 32 < 8 * warps;
 }
@@ -447,7 +450,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (which < 0) {
         // first guess: the wavefront pays where rays recurse and the frame is big enough to amortise its launches
         const int guess = (s->has_secondary && n_px >= (1u << 19)) ? 1 : 0;
-        const bool three = forced_lpp(s) < 0 && lpp2_candidate(s, n_px);
+        const bool three = forced_lpp(s) < 0 && mixed_candidate(s, n_px);
         if (s->frames < 4) {
             which = (s->frames & 1) ? 1 - guess : guess;  // two frames each: the first one is cold
         } else if (three && s->frames < 6) {
@@ -458,7 +461,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         }
     }
     int lpp = forced_lpp(s);
-    if (lpp < 0) lpp = which == 2 ? 2 : 1;
+    if (lpp < 0) lpp = which == 2 ? 0 : 1;
     const int slot = which == 2 ? 2 : 0;  // where a megakernel frame's time is recorded
     s->frames++;
     if (which == 1) {
@@ -489,7 +492,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             s->d_tile_cost = s->d_tile_order = nullptr;
             s->tile_cap = 0;
             // costs, then the scratch counts of tile_order.cu (4 per 1024 tiles)
-            CUDA_TRY(cudaMalloc(&s->d_tile_cost, (n_tiles + 4 * (n_tiles / 1024 + 1)) * sizeof(unsigned)));
+            CUDA_TRY(cudaMalloc(&s->d_tile_cost, (n_tiles + 4 * (n_tiles / 1024 + 1) + 1) * sizeof(unsigned)));
             CUDA_TRY(cudaMalloc(&s->d_tile_order, n_tiles * sizeof(unsigned)));
             s->tile_cap = n_tiles;
             s->order_tiles = 0;
@@ -497,10 +500,12 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         CUDA_TRY(cudaMemsetAsync(s->d_tile_cost, 0, n_tiles * sizeof(unsigned), stream));
         P.tile_cost = s->d_tile_cost;
         P.tile_order = s->order_tiles == n_tiles ? s->d_tile_order : nullptr;
+        P.heavy_tiles = s->d_tile_cost + n_tiles + 4 * ((n_tiles + 1023) / 1024);
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
-    P.n_items *= (unsigned long long)lpp;
+    if (lpp == 0 && !P.tile_order) lpp = 1;  // mixed needs the order of a previous frame
+    P.n_items *= (unsigned long long)(lpp ? lpp : 1);
     CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_render_mesh(s->d, P, lpp, s->grid, s->smem, stream)
                                              : launch_render_analytic(s->d, P, lpp, s->grid, s->smem, stream)));
     CUDA_TRY(cudaEventRecord(s->ev1, stream));
@@ -525,7 +530,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         stats->pixels = P.rows * cam->hsize;
         stats->kernel_ms = ms;
         stats->launches = lpt ? 3 : 1;  // render_kernel (+ the two kernels of tile_order.cu)
-        stats->kernel = lpp > 1 ? 2u : 0u;
+        stats->kernel = lpp != 1 ? 2u : 0u;
         stats->shadow_rays_culled = c[5];
     }
     if (s->best_ms[slot] < 0.0f || ms < s->best_ms[slot]) s->best_ms[slot] = ms;

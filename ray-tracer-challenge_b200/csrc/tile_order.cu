@@ -49,7 +49,8 @@ __global__ void __launch_bounds__(T) tile_count_kernel(const unsigned* __restric
 }
 
 __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
-                                                         const unsigned* __restrict__ counts, unsigned* __restrict__ order, unsigned n) {
+                                                         const unsigned* __restrict__ counts, unsigned* __restrict__ order,
+                                                         unsigned* __restrict__ heavy, unsigned n) {
     __shared__ unsigned s_base[4];           // where this block's tiles of bucket b start
     __shared__ unsigned s_warp[4][T / 32];   // tiles of bucket b in each warp, then their exclusive prefix
     __shared__ unsigned s_red[T / 32];
@@ -71,6 +72,7 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
         __syncthreads();
     }
     (void)total;
+    if (blockIdx.x == 0 && tid == 0) *heavy = s_base[1];  // block 0: all of bucket 0 (cost >= 8x the mean) lies before its bucket 1
     const unsigned i = blockIdx.x * T + tid;
     const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
     unsigned rank = 0;  // among the tiles of my bucket in my warp
@@ -95,13 +97,13 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
 }
 }  // namespace
 
-// scratch: 4 * ceil(n_tiles / 1024) unsigned; sum: the render kernel's sum of all tile costs (device memory)
+// scratch: 4 * ceil(n_tiles / 1024) + 1 unsigned (the last one receives the number of tiles in bucket 0); sum: the render kernel's sum of all tile costs (device memory)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
                       cudaStream_t stream) {
     if (!n_tiles) return 0;
     const unsigned blocks = (n_tiles + T - 1) / T;
     tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles);
-    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, n_tiles);
+    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, scratch + 4 * blocks, n_tiles);
     return (int)cudaGetLastError();
 }
 

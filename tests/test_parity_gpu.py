@@ -195,17 +195,22 @@ def test_lanes_per_pixel_are_bit_identical(pkg, name):
     out = {}
     try:
         os.environ["RTC_KERNEL"] = "mega"
-        for lpp in (1, 2, 4):
+        for lpp in (1, 2, 4, 0):  # 0 = mixed: four lanes on the tiles the previous frame found expensive
             os.environ["RTC_LPP"] = str(lpp)
-            c = info.camera.render(info.world)
-            p = info.camera.render(info.world, partition=(8, 1, 3))
-            r8, _ = info.camera.render_rgba8(info.world)
+            # twice each: the second frame of a size is rendered in the order of the first one's tile costs
+            # (tile_order.cu), which is what the mixed mode takes its expensive tiles from
+            for _ in range(2):
+                c = info.camera.render(info.world)
+            for _ in range(2):
+                p = info.camera.render(info.world, partition=(8, 1, 3))
+            for _ in range(2):
+                r8, _ = info.camera.render_rgba8(info.world)
             out[lpp] = (c.pixels.copy(), p.pixels.copy(), r8.copy(), c.stats.as_dict())
     finally:
         os.environ.pop("RTC_KERNEL", None)
         os.environ.pop("RTC_LPP", None)
     assert out[1][0].any()
-    for lpp in (2, 4):
+    for lpp in (2, 4, 0):
         for k in range(3):
             assert np.array_equal(out[1][k], out[lpp][k])
         for key in ("primary", "shadow", "secondary", "shadow_culled"):
@@ -213,8 +218,9 @@ def test_lanes_per_pixel_are_bit_identical(pkg, name):
 
 
 def test_small_partitions_measure_two_lanes_per_pixel(pkg):
-    """A partition that leaves the machine underfilled renders frames 5-6 with two lanes per pixel (third candidate
-    of the library's first-frames measurement): every frame of the sequence is the same frame."""
+    """A partition that leaves the machine underfilled renders frames 5-6 with the mixed kernel (four lanes per pixel
+    on the tiles the previous frame found expensive; third candidate of the library's first-frames measurement):
+    every frame of the sequence is the same frame."""
     s = scenes.shipped_scene("dragons")
     if s is None:
         pytest.skip("reference assets not staged")

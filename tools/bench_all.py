@@ -84,7 +84,7 @@ def main():
         print(json.dumps({"roofline": roof, "scene": name, "width": cam.hsize, "height": cam.vsize, "kernel_ms": round(ms, 4),
                           "min_ms": round(times[0], 4), "rays": st.rays, "Mrays_s": round(st.rays / ms / 1e3, 1),
                           "primary": st.primary_rays, "shadow": st.shadow_rays, "secondary": st.secondary_rays, "shadow_culled": st.shadow_rays_culled,
-                          "kernel": ("megakernel", "wavefront", "megakernel, 2 lanes per pixel")[st.kernel] + " (%d launches)" % st.launches, "setup_s": round(setup, 3), "checksum": float(buf.sum().item())}), flush=True)
+                          "kernel": ("megakernel", "wavefront", "megakernel, several lanes per pixel")[st.kernel] + " (%d launches)" % st.launches, "setup_s": round(setup, 3), "checksum": float(buf.sum().item())}), flush=True)
         info.world.close()
 
 

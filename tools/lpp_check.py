@@ -22,7 +22,7 @@ def main():
         info = pkg.parse_scene(text, assets, w, h)
         cam = info.camera
         frames = {}
-        for lpp in (1, 2, 4):
+        for lpp in (1, 2, 4, 0):  # 0 = mixed: four lanes per pixel on the tiles the last frame found expensive
             os.environ["RTC_LPP"] = str(lpp)
             frame = torch.zeros((cam.vsize, cam.hsize, 3), dtype=torch.float64, device="cuda")
             out = {"scene": name, "lpp": lpp}
