@@ -3,6 +3,7 @@
 
 #include <cstring>
 #include <map>
+#include <unordered_map>
 #include <stdexcept>
 
 namespace rtc {
@@ -184,22 +185,66 @@ bool always_pass(const BBox& b) {
     return axis(b.min.x, b.max.x) && axis(b.min.y, b.max.y) && axis(b.min.z, b.max.z);
 }
 
-// Is `box` a superset of the true extent of every leaf below `s`?
-bool covers(const BBox& box, const Shape& s) {
-    if (s.kind == ShapeKind::Group) {
-        for (const Shape& c : s.children)
-            if (!covers(box, c)) return false;
-        return true;
+// Is `box` a superset of the true extent of every leaf below `s`?  Per leaf the test is
+//   le(box.min, w.min) && le(w.max, box.max) on every axis,  le(a, b) = a <= b + 1e-9 (|a| + |b| + 1e-300)
+// (box-of-box vs direct transform differ by rounding only; a few ulps of slack), w = the leaf's parent-space bounds.
+// le is monotone in either argument (b + 1e-9 |b| grows with b, a - 1e-9 |a| with a, and rounding keeps order), so
+// "for every leaf" equals the same test on the component-wise min of the w.min and max of the w.max of the subtree:
+// the extents are gathered ONCE per node, bottom-up (a dragon's 23,490 triangles sit under ~8,000 groups 13 deep; asking
+// every group for all its leaves again was 0.5 s of the 0.75 s flattening of dragons.json).
+struct Extent {
+    bool ok = true;   // every leaf is bounded with finite bounds
+    size_t leaves = 0;
+    double mn[3] = {kInf, kInf, kInf}, mx[3] = {-kInf, -kInf, -kInf};
+    void merge(const Extent& e) {
+        ok = ok && e.ok;
+        leaves += e.leaves;
+        for (int k = 0; k < 3; k++) {
+            mn[k] = std::fmin(mn[k], e.mn[k]);
+            mx[k] = std::fmax(mx[k], e.mx[k]);
+        }
     }
-    if (s.kind == ShapeKind::Csg) return covers(box, *s.left) && covers(box, *s.right);
-    if (s.kind == ShapeKind::Test) return true;
-    if (!leaf_bounded(s)) return false;
+};
+thread_local std::unordered_map<const Shape*, Extent> g_extent;  // groups and CSG nodes of the world being flattened
+
+Extent extent_of(const Shape& s) {
+    if (s.kind == ShapeKind::Group || s.kind == ShapeKind::Csg) {
+        auto it = g_extent.find(&s);
+        if (it != g_extent.end()) return it->second;
+        Extent e;
+        if (s.kind == ShapeKind::Group) {
+            for (const Shape& c : s.children) e.merge(extent_of(c));
+        } else {
+            e.merge(extent_of(*s.left));
+            e.merge(extent_of(*s.right));
+        }
+        g_extent.emplace(&s, e);
+        return e;
+    }
+    Extent e;
+    if (s.kind == ShapeKind::Test) return e;
+    e.leaves = 1;
+    if (!leaf_bounded(s)) {
+        e.ok = false;
+        return e;
+    }
     BBox w = s.parent_space_bounds();
-    if (!finite3(w.min) || !finite3(w.max)) return false;
-    // box-of-box vs direct transform differ by rounding only; allow a few ulps of slack
+    if (!finite3(w.min) || !finite3(w.max)) {
+        e.ok = false;
+        return e;
+    }
+    e.mn[0] = w.min.x, e.mn[1] = w.min.y, e.mn[2] = w.min.z;
+    e.mx[0] = w.max.x, e.mx[1] = w.max.y, e.mx[2] = w.max.z;
+    return e;
+}
+
+bool covers(const BBox& box, const Shape& s) {
+    const Extent e = extent_of(s);
+    if (!e.ok) return false;
+    if (e.leaves == 0) return true;
     auto le = [](double a, double b) { return a <= b + 1e-9 * (std::fabs(a) + std::fabs(b) + 1e-300); };
-    return le(box.min.x, w.min.x) && le(box.min.y, w.min.y) && le(box.min.z, w.min.z) && le(w.max.x, box.max.x) &&
-           le(w.max.y, box.max.y) && le(w.max.z, box.max.z);
+    return le(box.min.x, e.mn[0]) && le(box.min.y, e.mn[1]) && le(box.min.z, e.mn[2]) && le(e.mx[0], box.max.x) &&
+           le(e.mx[1], box.max.y) && le(e.mx[2], box.max.z);
 }
 
 struct Walker {
@@ -333,7 +378,9 @@ std::vector<uint8_t> flatten_world(const World& world) {
         b.lights.push_back(rec);
     }
     Walker w{b};
+    g_extent.clear();
     for (const Shape& s : world.objects) w.walk(s);
+    g_extent.clear();
 
     rtc_blob_header h{};
     h.magic = RTC_BLOB_MAGIC;

@@ -183,10 +183,14 @@ void Shape::partition_children(std::vector<Shape>& left, std::vector<Shape>& rig
 }
 
 void Shape::make_subgroup(std::vector<Shape>& members) {
+    // add_child (group.zig:75-78) for every member, in order: the box is merged in the same order (same bits);
+    // the members themselves change hands as one vector instead of one Shape move at a time
     Shape sub = Shape::group();
-    sub.children.reserve(members.size());
-    for (Shape& m : members) sub.add_child(std::move(m));
-    add_child(std::move(sub));
+    for (const Shape& m : members) sub.bbox.merge(m.parent_space_bounds());
+    sub.children = std::move(members);
+    members.clear();
+    bbox.merge(sub.parent_space_bounds());
+    children.push_back(std::move(sub));
 }
 
 void Shape::divide(size_t threshold) {

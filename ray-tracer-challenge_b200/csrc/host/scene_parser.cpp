@@ -22,7 +22,17 @@ struct Ctx {
     std::map<std::string, const Json*> definitions;
     std::vector<std::shared_ptr<const Image>> images;
     std::vector<std::shared_ptr<Image>> missing;  // stand-ins filled after the whole scene is read
+    std::map<std::string, Shape> obj_groups;      // OBJ files parsed so far, by "file|normalize"
 };
+
+void stamp_triangles(Shape& s, const Material& mat, bool casts_shadow) {
+    if (s.kind == ShapeKind::Group) {
+        for (Shape& c : s.children) stamp_triangles(c, mat, casts_shadow);
+    } else {
+        s.material = mat;
+        s.casts_shadow = casts_shadow;
+    }
+}
 
 void vec3(const Json& j, double out[3]) {
     const auto& a = j.array();
@@ -232,14 +242,24 @@ Shape parse_object(Ctx& cx, const Json& obj, const Inherited& inherited) {  // s
             return parent;
         }
         if (k == "from-obj") {
-            std::string text = cx.load(v.at("file").string());
-            ObjParser parser;
-            ObjInherited st;
-            st.has_material = info.has_material;
-            st.material = info.material;
-            st.casts_shadow = info.casts_shadow;
-            parser.load_obj(text, st, opt_bool(v, "normalize", true));
-            return parser.to_group();
+            // The reference reads and parses the file again for every object made from it (scene.zig:455-488: six
+            // times data/dragon.obj in dragons.json).  Here the file is parsed once per (file, normalize) with no
+            // inherited state; every object takes a copy of that group and stamps its own material / casts-shadow on
+            // the triangles -- the only two things obj.zig:101-160 takes from the inherited state.
+            const std::string file = v.at("file").string();
+            const bool normalize = opt_bool(v, "normalize", true);
+            const std::string key = file + (normalize ? "|n" : "|r");
+            auto it = cx.obj_groups.find(key);
+            if (it == cx.obj_groups.end()) {
+                ObjParser parser;
+                parser.load_obj(cx.load(file), ObjInherited{}, normalize);
+                it = cx.obj_groups.emplace(key, parser.to_group()).first;
+            }
+            Shape g = it->second;
+            const Material mat = info.has_material ? info.material : Material();
+            const bool casts = info.casts_shadow < 0 ? true : (info.casts_shadow != 0);
+            stamp_triangles(g, mat, casts);
+            return g;
         }
         if (k == "sphere") return Shape::sphere();
         if (k == "plane") return Shape::plane();
@@ -291,7 +311,7 @@ Shape parse_object(Ctx& cx, const Json& obj, const Inherited& inherited) {  // s
 SceneInfo parse_scene(const std::string& json_text, const FileLoader& load, long width_override,
                       long height_override) {
     Json root = JsonParser(json_text).parse();
-    Ctx cx{load, {}, {}, {}};
+    Ctx cx{load, {}, {}, {}, {}};
     if (const Json* defs = root.find("shape-definitions"))
         for (const Json& d : defs->array()) cx.definitions[d.at("name").string()] = &d.at("value");
 

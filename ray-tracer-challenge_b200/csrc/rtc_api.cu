@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/rtc_b200.h: scene upload, render calls, host loader.
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cmath>
 #include <algorithm>
 #include <cstdio>
@@ -649,8 +650,14 @@ int rtc_load_scene_json(const char* json_text, const char* asset_dir, long width
                         size_t* nbytes_out, rtc_camera* cam_out) {
     if (!json_text || !blob_out || !nbytes_out || !cam_out) return fail(RTC_ERR_INVALID, "rtc_load_scene_json: NULL argument");
     try {
+        auto T0 = std::chrono::steady_clock::now();
         SceneInfo si = parse_scene(json_text, directory_loader(asset_dir ? asset_dir : ""), width, height);
+        auto T1 = std::chrono::steady_clock::now();
         std::vector<uint8_t> blob = flatten_world(si.world);
+        auto T2 = std::chrono::steady_clock::now();
+        if (std::getenv("RTC_LOAD_TIMING"))
+            std::fprintf(stderr, "load: parse %.3f flatten %.3f s\n", std::chrono::duration<double>(T1 - T0).count(),
+                         std::chrono::duration<double>(T2 - T1).count());
         void* p = std::malloc(blob.size());
         if (!p) return fail(RTC_ERR_INVALID, "out of memory");
         std::memcpy(p, blob.data(), blob.size());
