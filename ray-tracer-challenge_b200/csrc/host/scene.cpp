@@ -166,19 +166,23 @@ void Shape::add_child(Shape child) {
 void Shape::partition_children(std::vector<Shape>& left, std::vector<Shape>& right) {
     BBox lb, rb;
     bbox.split(lb, rb);
-    std::vector<Shape> keep;
-    left.reserve(children.size());
-    right.reserve(children.size());
-    keep.reserve(children.size());
-    for (Shape& c : children) {
-        BBox cb = c.parent_space_bounds();
-        if (lb.contains_box(cb))
-            left.push_back(std::move(c));
-        else if (rb.contains_box(cb))
-            right.push_back(std::move(c));
-        else
-            keep.push_back(std::move(c));
+    // classify first (same tests, same order as group.zig:92-112), then move every child exactly once into a vector of
+    // exactly its final size; a group whose children all straddle the split is left as it is
+    std::vector<unsigned char> side(children.size());
+    size_t n_left = 0, n_right = 0;
+    for (size_t i = 0; i < children.size(); i++) {
+        BBox cb = children[i].parent_space_bounds();
+        side[i] = lb.contains_box(cb) ? 0 : rb.contains_box(cb) ? 1 : 2;
+        n_left += side[i] == 0;
+        n_right += side[i] == 1;
     }
+    if (n_left == 0 && n_right == 0) return;
+    std::vector<Shape> keep;
+    left.reserve(n_left);
+    right.reserve(n_right);
+    keep.reserve(children.size() - n_left - n_right);
+    for (size_t i = 0; i < children.size(); i++)
+        (side[i] == 0 ? left : side[i] == 1 ? right : keep).push_back(std::move(children[i]));
     children = std::move(keep);
 }
 
