@@ -27,6 +27,7 @@ namespace {
 constexpr int T = 1024;
 
 __device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum) {
+    if (sum == 0) return 3;  // nothing measured (every tile below one tick): keep the plain order
     const unsigned long long c = (unsigned long long)cost * n;  // cost / mean = c / sum; cost < 2^32, n < 2^24
     return c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
 }
