@@ -152,7 +152,10 @@ def base_line(args, n):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "scenes/dragons.json 1920x1080 depth 5 (6 x dragon.obj, 140,940 smooth triangles, "
                                    "4 lights); the scene file IS the input, there is no random data",
-                       "l2": "flushed between steps (256 MiB memset)", "partition": "interleaved %d-row tiles" % TILE_ROWS}}
+                       "l2": "flushed between steps (256 MiB memset)", "partition": "interleaved %d-row tiles" % TILE_ROWS,
+                       "tile_order": "device-resident frames: tiles handed out in the order of their cost in the previous frame "
+                                     "(scheduling only: every ray of every pixel is traced in every step, frames bit-identical; "
+                                     "RTC_LPT=0 for the plain order); host canvases: strided row order"}}
 
 
 def run_reference(args, rank):
