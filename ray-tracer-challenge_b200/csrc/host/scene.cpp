@@ -1,4 +1,6 @@
 // Build-time operations on the host scene model (see scene.hpp for the reference map).
+#include <cstdint>
+#include <memory>
 #include "scene.hpp"
 
 #include <cstring>
@@ -197,13 +199,81 @@ void Shape::make_subgroup(std::vector<Shape>& members) {
     children.push_back(std::move(sub));
 }
 
+// divide() of a whole subtree of NEW subgroups, planned on child indices first and built afterwards, so that a leaf
+// changes hands once instead of once per level (a Shape is ~0.9 kB; a dragon's 23,490 triangles end up 13 levels deep:
+// moving them level by level was half of the scene set-up time).  Same tests in the same order as the level-by-level
+// form -- partition_children / make_subgroup above, which stay for the reference's own tests of them: a subgroup's box
+// is the merge of its members' parent-space bounds in child order (its transform is the identity, so those bounds are
+// the ones the parent saw), it is split only when it holds >= threshold members, and its children are the members
+// that straddle the split, in order, followed by the left and the right subgroup.
+namespace {
+struct DivPlan {
+    std::vector<uint32_t> keep;
+    std::unique_ptr<DivPlan> left, right;
+    BBox left_box, right_box;
+};
+
+std::unique_ptr<DivPlan> plan_divide(const std::vector<BBox>& pb, std::vector<uint32_t> members, const BBox& box, size_t threshold) {
+    auto n = std::make_unique<DivPlan>();
+    if (members.size() < threshold) {
+        n->keep = std::move(members);
+        return n;
+    }
+    BBox lb, rb;
+    box.split(lb, rb);
+    std::vector<uint32_t> l, r;
+    for (uint32_t i : members) {
+        if (lb.contains_box(pb[i])) l.push_back(i);
+        else if (rb.contains_box(pb[i])) r.push_back(i);
+        else n->keep.push_back(i);
+    }
+    if (!l.empty()) {
+        for (uint32_t i : l) n->left_box.merge(pb[i]);
+        n->left = plan_divide(pb, std::move(l), n->left_box, threshold);
+    }
+    if (!r.empty()) {
+        for (uint32_t i : r) n->right_box.merge(pb[i]);
+        n->right = plan_divide(pb, std::move(r), n->right_box, threshold);
+    }
+    return n;
+}
+
+void build_divided(Shape& g, const DivPlan& n, const BBox& lbox, const BBox& rbox, std::vector<Shape>& pool, size_t threshold);
+
+void add_planned_subgroup(Shape& g, const DivPlan& sub_plan, const BBox& box, std::vector<Shape>& pool, size_t threshold) {
+    Shape sub = Shape::group();
+    sub.bbox = box;
+    build_divided(sub, sub_plan, sub_plan.left_box, sub_plan.right_box, pool, threshold);
+    g.bbox.merge(sub.parent_space_bounds());  // add_child (group.zig:75-78)
+    g.children.push_back(std::move(sub));
+}
+
+void build_divided(Shape& g, const DivPlan& n, const BBox& lbox, const BBox& rbox, std::vector<Shape>& pool, size_t threshold) {
+    g.children.reserve(n.keep.size() + (n.left ? 1 : 0) + (n.right ? 1 : 0));
+    for (uint32_t i : n.keep) g.children.push_back(std::move(pool[i]));
+    if (n.left) add_planned_subgroup(g, *n.left, lbox, pool, threshold);
+    if (n.right) add_planned_subgroup(g, *n.right, rbox, pool, threshold);
+    // the members that stayed may be groups or CSG objects of their own (the new subgroups are planned already)
+    for (size_t k = 0; k < n.keep.size(); k++) g.children[k].divide(threshold);
+}
+}  // namespace
+
 void Shape::divide(size_t threshold) {
     if (kind == ShapeKind::Group) {
         if (children.size() >= threshold) {
-            std::vector<Shape> l, r;
-            partition_children(l, r);
-            if (!l.empty()) make_subgroup(l);
-            if (!r.empty()) make_subgroup(r);
+            std::vector<BBox> pb(children.size());
+            std::vector<uint32_t> all(children.size());
+            for (size_t i = 0; i < children.size(); i++) {
+                pb[i] = children[i].parent_space_bounds();
+                all[i] = (uint32_t)i;
+            }
+            std::unique_ptr<DivPlan> plan = plan_divide(pb, std::move(all), bbox, threshold);
+            if (plan->left || plan->right) {
+                std::vector<Shape> pool = std::move(children);
+                children.clear();
+                build_divided(*this, *plan, plan->left_box, plan->right_box, pool, threshold);
+                return;
+            }
         }
         for (Shape& c : children) c.divide(threshold);
     } else if (kind == ShapeKind::Csg) {
