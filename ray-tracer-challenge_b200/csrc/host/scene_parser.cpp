@@ -2,7 +2,11 @@
 // Order of operations inside parse_object is the reference's (scene.zig:440-591):
 //   inherit -> construct variant (children parsed WITHOUT the parent transform) -> setTransform
 //   (push-down) -> material / casts_shadow -> divide(8)   ... at EVERY nesting level.
+#include <algorithm>
+#include <atomic>
+#include <exception>
 #include <map>
+#include <thread>
 
 #include "json.hpp"
 #include "loader.hpp"
@@ -23,7 +27,41 @@ struct Ctx {
     std::vector<std::shared_ptr<const Image>> images;
     std::vector<std::shared_ptr<Image>> missing;  // stand-ins filled after the whole scene is read
     std::map<std::string, Shape> obj_groups;      // OBJ files parsed so far, by "file|normalize"
+    // Images met so far, not yet decoded: nothing in the parse looks inside an image, so the files are inflated side by
+    // side once the scene is read (skybox.json: five 2048x2048 PNGs) instead of one after the other where they appear.
+    struct Pending {
+        std::shared_ptr<Image> img;
+        std::string bytes, file;
+    };
+    std::vector<Pending> pending;
 };
+
+// Decodes cx.pending on all host cores; the error reported is the one of the FIRST failing file in scene order, which is
+// the one a decode-as-you-go parse would have stopped at.
+void decode_pending(Ctx& cx) {
+    const size_t n = cx.pending.size();
+    if (n == 0) return;
+    std::vector<std::exception_ptr> errors(n);
+    std::atomic<size_t> next{0};
+    auto work = [&] {
+        for (size_t i = next++; i < n; i = next++) {
+            try {
+                std::shared_ptr<Image> d = decode_image(cx.pending[i].bytes, cx.pending[i].file);
+                *cx.pending[i].img = std::move(*d);
+            } catch (...) {
+                errors[i] = std::current_exception();
+            }
+        }
+    };
+    const size_t n_threads = std::min<size_t>(n, std::max(1u, std::thread::hardware_concurrency()));
+    std::vector<std::thread> pool;
+    for (size_t t = 1; t < n_threads; t++) pool.emplace_back(work);
+    work();
+    for (std::thread& t : pool) t.join();
+    cx.pending.clear();
+    for (const std::exception_ptr& e : errors)
+        if (e) std::rethrow_exception(e);
+}
 
 void stamp_triangles(Shape& s, const Material& mat, bool casts_shadow) {
     if (s.kind == ShapeKind::Group) {
@@ -107,8 +145,10 @@ UvPattern parse_uv_pattern(Ctx& cx, const Json& j) {  // scene.zig:243-298
             found = false;
         }
         if (found) {
-            auto img = decode_image(bytes, file);
+            auto img = std::make_shared<Image>();
+            img->name = file;
             cx.images.push_back(img);
+            cx.pending.push_back({img, std::move(bytes), file});
             uv.image = img;
         } else {
             // SURVEY F6 (data/lancellotti-posy.png absent from the mount): placeholder, filled later.
@@ -311,7 +351,7 @@ Shape parse_object(Ctx& cx, const Json& obj, const Inherited& inherited) {  // s
 SceneInfo parse_scene(const std::string& json_text, const FileLoader& load, long width_override,
                       long height_override) {
     Json root = JsonParser(json_text).parse();
-    Ctx cx{load, {}, {}, {}, {}};
+    Ctx cx{load, {}, {}, {}, {}, {}};
     if (const Json* defs = root.find("shape-definitions"))
         for (const Json& d : defs->array()) cx.definitions[d.at("name").string()] = &d.at("value");
 
@@ -330,15 +370,21 @@ SceneInfo parse_scene(const std::string& json_text, const FileLoader& load, long
     out.camera.up = Tuple::vec3(u[0], u[1], u[2]);
     out.camera.set_transform(Mat4::view_transform(out.camera.from, out.camera.to, out.camera.up));
 
-    for (const Json& o : root.at("objects").array()) out.world.objects.push_back(parse_object(cx, o, Inherited{}));
-    for (const Json& l : root.at("lights").array()) {
-        const auto& kv = l.single();
-        if (kv.first != "point-light") throw JsonError("unknown light");
-        double p[3], i[3];
-        vec3(kv.second.at("position"), p);
-        vec3(kv.second.at("intensity"), i);
-        out.world.lights.push_back({Tuple::point(p[0], p[1], p[2]), {i[0], i[1], i[2]}});
+    try {
+        for (const Json& o : root.at("objects").array()) out.world.objects.push_back(parse_object(cx, o, Inherited{}));
+        for (const Json& l : root.at("lights").array()) {
+            const auto& kv = l.single();
+            if (kv.first != "point-light") throw JsonError("unknown light");
+            double p[3], i[3];
+            vec3(kv.second.at("position"), p);
+            vec3(kv.second.at("intensity"), i);
+            out.world.lights.push_back({Tuple::point(p[0], p[1], p[2]), {i[0], i[1], i[2]}});
+        }
+    } catch (...) {
+        decode_pending(cx);  // an image met BEFORE the failing element that does not decode is the earlier error
+        throw;
     }
+    decode_pending(cx);
     for (auto& m : cx.missing) {
         auto s = standin_image(cx.images, m->name);
         m->width = s->width;
