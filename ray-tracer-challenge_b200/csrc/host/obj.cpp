@@ -132,26 +132,45 @@ bool ObjParser::handle_line(const std::string& line, const ObjInherited& st) {
 }
 
 void ObjParser::load_obj(const std::string& text, const ObjInherited& st, bool normalize) {
-    std::vector<std::string> lines = tokenize(text, '\n');
+    // lines = the non-empty pieces between '\n' (std.mem.tokenizeScalar); walked in place, one reused buffer
+    auto for_each_line = [&](auto&& fn) {
+        std::string line;
+        size_t i = 0;
+        while (i < text.size()) {
+            while (i < text.size() && text[i] == '\n') i++;
+            size_t j = i;
+            while (j < text.size() && text[j] != '\n') j++;
+            if (j > i) {
+                line.assign(text, i, j - i);
+                fn(line);
+            }
+            i = j;
+        }
+    };
     if (normalize) {  // obj.zig:198-268
         double mn[3] = {kInf, kInf, kInf}, mx[3] = {-kInf, -kInf, -kInf};
-        for (const std::string& line : lines) {
+        for_each_line([&](const std::string& line) {
+            // only lines whose first token is exactly "v" count: look before splitting the whole line
+            size_t k = 0;
+            while (k < line.size() && line[k] == ' ') k++;
+            if (k >= line.size() || line[k] != 'v' || (k + 1 < line.size() && line[k + 1] != ' ')) return;
             std::vector<std::string> tok = tokenize(line, ' ');
-            if (tok.empty() || tok[0] != "v") continue;
-            for (int k = 0; k < 3; k++) {
+            if (tok.empty() || tok[0] != "v") return;
+            for (int c = 0; c < 3; c++) {
                 double v;
-                if ((size_t)(k + 1) < tok.size() && parse_float(tok[k + 1], v)) {
-                    if (v < mn[k]) mn[k] = v;
-                    if (v > mx[k]) mx[k] = v;
+                if ((size_t)(c + 1) < tok.size() && parse_float(tok[c + 1], v)) {
+                    if (v < mn[c]) mn[c] = v;
+                    if (v > mx[c]) mx[c] = v;
                 }
             }
-        }
+        });
         double sx = mx[0] - mn[0], sy = mx[1] - mn[1], sz = mx[2] - mn[2];
         offset = Tuple::vec3(mn[0] + 0.5 * sx, mn[1] + 0.5 * sy, mn[2] + 0.5 * sz);
         scale = 0.5 * std::fmax(sx, std::fmax(sy, sz));
     }
-    for (const std::string& line : lines)
+    for_each_line([&](const std::string& line) {
         if (!handle_line(line, st)) lines_ignored++;
+    });
 }
 
 }  // namespace rtc
