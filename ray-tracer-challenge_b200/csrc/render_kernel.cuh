@@ -76,6 +76,8 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 // the rays of one trip through the world are alike and the traversal loop runs with far fewer idle lanes.  Measured
 // on B200 (kernel ms at 1 / 8 / 16 / 32): dragons 1.52 / 1.40 / 1.37 / 1.23, cover 4.8 / 4.2 / 3.7 / 3.3, fresnel
 // 0.96 / 0.92 / 0.89 / 0.83, teapot 0.60 throughout.  (1 = every lane for itself, the first design.)
+// (The lanes-per-pixel instantiations below rely on whole-warp refills: since they exist, only 32 compiles; the
+// measurements above were taken with -DRTC_REFILL_MIN=... variant builds of the one-lane kernel.)
 #ifndef RTC_REFILL_MIN
 #define RTC_REFILL_MIN 32
 #endif
