@@ -58,6 +58,19 @@ int rtc_device_count(void);
 /* Selects the CUDA device used by scenes created afterwards on this thread (default 0). */
 int rtc_set_device(int device);
 
+/* What rtc_scene_create builds out of a blob, without touching a device (host-side validation + mesh instancing +
+ * BVH build only; runs anywhere): a World(f64) handed to Camera.render (world.zig:20-25) becomes n_prims analytic
+ * top-level leaves, n_csg CSG programs and n_meshes triangle-mesh INSTANCES over n_geometries distinct BVHs (objects
+ * made from the same OBJ data share one: scene.zig:455-488 re-parses the file per object instead). */
+typedef struct rtc_scene_info {
+    uint32_t n_prims, n_meshes, n_geometries, n_csg;
+    uint64_t n_bvh_nodes, n_mesh_triangles; /* of the distinct geometries */
+    uint64_t device_bytes;                  /* size of the one slab the scene occupies in HBM */
+    uint32_t bvh_max_depth, n_leaves;
+    double build_seconds;
+} rtc_scene_info;
+int rtc_blob_inspect(const void* blob, size_t nbytes, rtc_scene_info* info_out);
+
 /* Scene lifetime.  The blob is copied; the caller may free it as soon as the call returns. */
 int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out);
 void rtc_scene_destroy(rtc_scene* scene);

@@ -39,6 +39,16 @@ class rtc_partition(ctypes.Structure):
     _fields_ = [("tile_rows", ctypes.c_uint32), ("part", ctypes.c_uint32), ("n_parts", ctypes.c_uint32)]
 
 
+class rtc_scene_info(ctypes.Structure):
+    _fields_ = [("n_prims", ctypes.c_uint32), ("n_meshes", ctypes.c_uint32), ("n_geometries", ctypes.c_uint32),
+                ("n_csg", ctypes.c_uint32), ("n_bvh_nodes", ctypes.c_uint64), ("n_mesh_triangles", ctypes.c_uint64),
+                ("device_bytes", ctypes.c_uint64), ("bvh_max_depth", ctypes.c_uint32), ("n_leaves", ctypes.c_uint32),
+                ("build_seconds", ctypes.c_double)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
 class rtc_stats(ctypes.Structure):
     _fields_ = [("primary_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64),
                 ("secondary_rays", ctypes.c_uint64), ("pixels", ctypes.c_uint64), ("kernel_ms", ctypes.c_float),
@@ -55,7 +65,7 @@ class rtc_stats(ctypes.Structure):
 
 
 # every symbol include/rtc_b200.h declares
-EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_scene_create", "rtc_scene_destroy",
+EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
            "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png"]
 # include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
@@ -78,6 +88,7 @@ def lib():
     L.rtc_last_error.restype = cp
     L.rtc_device_count.restype = ctypes.c_int
     L.rtc_set_device.argtypes = [ctypes.c_int]
+    L.rtc_blob_inspect.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(rtc_scene_info)]
     L.rtc_scene_create.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
     L.rtc_scene_destroy.argtypes = [vp]
     L.rtc_scene_destroy.restype = None
@@ -139,6 +150,13 @@ def load_blob(json_text, asset_dir="", width=0, height=0):
     finally:
         L.rtc_blob_free(blob)
     return data, cam
+
+
+def inspect_blob(blob):
+    """What rtc_scene_create would build from this blob (prims, mesh instances, shared geometries, BVH size): host only."""
+    info = rtc_scene_info()
+    _check(lib().rtc_blob_inspect(blob, len(blob), ctypes.byref(info)))
+    return info
 
 
 class _Pinned:

@@ -4,11 +4,18 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 namespace rtc {
 namespace {
 
-constexpr int kLeafMax = 4;
+// Triangles per leaf: the traversal encodes a leaf as (first << 3) | count, so at most 7.  RTC_BVH_LEAF=1..7 overrides
+// the default for experiments (profiles/README.md: leaf size against kernel time).
+const int kLeafMax = [] {
+    const char* e = std::getenv("RTC_BVH_LEAF");
+    int v = e ? std::atoi(e) : 4;
+    return v >= 1 && v <= 7 ? v : 4;
+}();
 constexpr int kBins = 16;
 constexpr int kSahDepthLimit = 40;  // beyond this depth split by median count (bounds total depth)
 

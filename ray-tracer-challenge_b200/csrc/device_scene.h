@@ -14,7 +14,8 @@ namespace rtc {
 // Triangle record in BVH leaf order, object space, f64 (triangle.zig:22-27).  80 bytes = 5 x 16.
 struct DTri {
     double p1[3], e1[3], e2[3];
-    int32_t leaf;  // rtc_leaf index: material / normals / tie-break order
+    int32_t leaf;  // rank of the triangle in its geometry's canonical order: DScene.mesh_leaf[DMesh.leaf_map + leaf] is
+                   // the rtc_leaf index (material / normals / tie-break order) in the instance being traversed
     int32_t pad;
 };
 static_assert(sizeof(DTri) == 80, "DTri must be 80 bytes");
@@ -28,7 +29,8 @@ struct BvhNode {
 };
 static_assert(sizeof(BvhNode) == 64, "BvhNode must be 64 bytes");
 
-// One mesh = all non-CSG triangles sharing a world->object matrix and a casts_shadow flag.
+// One mesh INSTANCE = all non-CSG triangles sharing a world->object matrix and a casts_shadow flag.  Instances with the
+// same object-space triangles share one geometry (BVH nodes + DTri records, scene_build.cpp): `root` is then the same.
 struct DMesh {
     int32_t transform;   // rtc_transform index
     uint32_t flags;      // RTC_CASTS_SHADOW
@@ -36,7 +38,8 @@ struct DMesh {
     int32_t n_tris;
     float lo[3], hi[3];  // object-space root box (outward rounded)
     float bound_abs[3];  // max |coordinate| of the root box per axis: scales the f32 slab error bound
-    float pad[3];
+    int32_t leaf_map;    // first entry of this instance in DScene.mesh_leaf (n_tris entries)
+    float pad[2];
     float wlo[3], whi[3];  // conservative WORLD-space box of the mesh, f32 rounded outward (pre-test before
     float pad2[2];         // the ray transform); +-inf when the transform is degenerate
 };
@@ -82,6 +85,7 @@ struct DScene {
     const DMesh* meshes;
     const BvhNode* bvh;
     const DTri* tris;
+    const int32_t* mesh_leaf;  // per instance: canonical triangle rank -> rtc_leaf index
     const int4* csg_prog;
     const DCsgRoot* csg_roots;
     int32_t n_lights, n_prims, n_meshes, n_csg;

@@ -95,7 +95,10 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 // dependent trips behind a pixel shrinks from 1 + n_lights per hit to 1 + ceil(n_lights / LPP), at the price of LPP
 // times the closest-hit work: a loss while there are enough pixels to fill the machine, a gain for the small
 // partitions of a multi-GPU frame, whose time is the chain of their most expensive tile (profiles/README.md).
-template <bool MESH, int LPP>
+// LEAN = the scene has no CSG objects, no guard boxes (hence no stray triangles among the prims) and only solid
+// patterns (rtc_api.cu lean_scene: dragons.json, teapot.json, cover.json ...): the instantiation carries none of that
+// code -- fewer instructions to fetch (the render loop is larger than the instruction cache) and fewer live registers.
+template <bool MESH, int LPP, bool LEAN>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
     static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");
     // LPP == 0 ("mixed"): four lanes per pixel on the tiles the last frame found expensive (the first *P.heavy_tiles
@@ -254,6 +257,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 q.t = RTC_INF;
                 q.leaf = -1;
                 q.a = q.b = 0.0;
+                q.c_leaf = 0;
             } else if (state == ST_SHADOW) {  // World.isShadowed (world.zig:126-135)
                 // over_point = point + normal * EPSILON, recomputed from the parked ray and hit
                 // (same operations as PreComputations.new, world.zig:219-224: same bits)
@@ -290,7 +294,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
 #ifdef RTC_TRIP_PROBE
         const long long probe_t0 = clock64();
 #endif
-        busy = trace_begin<MESH>(q, S, trav, &err, state != ST_IDLE && !skip);
+        busy = trace_begin<MESH, LEAN>(q, S, trav, &err, state != ST_IDLE && !skip);
         // every mesh through ONE warp-wide traversal loop; the full-mask votes are the points where
         // the warp reconverges, so inner-node steps and triangle tests each run with all traversing lanes
         if constexpr (MESH) {
@@ -328,8 +332,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 const double* nrm = nullptr;
                 if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
                     nrm = S.normals[L.triangle].n;
-                    if (kind == RTC_SMOOTH_TRIANGLE) {
-                        // u,v of a triangle found outside the mesh path: same ray, same test, same values
+                    if (!LEAN && kind == RTC_SMOOTH_TRIANGLE && !q.c_leaf) {
+                        // u,v of a smooth triangle that is a CSG operand: same ray, same test, same values
                         const rtc_triangle& T = S.blob_tris[L.triangle];
                         double tt;
                         tri_intersect(v3(T.p1[0], T.p1[1], T.p1[2]), v3(T.e1[0], T.e1[1], T.e1[2]),
@@ -345,7 +349,12 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 const rtc_material& M = S.materials[h_mat];
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
-                pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
+                if constexpr (LEAN) {  // every pattern is solid (solid.zig): its colour, whatever the point
+                    const double* pc = S.patterns[M.pattern].color;
+                    pk_st(pk, PK_COLOR, v3(__ldg(pc), __ldg(pc + 1), __ldg(pc + 2)));
+                } else {
+                    pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
+                }
                 h_light = (int)sub;
                 PK(PK_N1) = 1.0;
                 PK(PK_N2) = 1.0;
@@ -398,7 +407,12 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 double v[3] = {c.x * P.scale, c.y * P.scale, c.z * P.scale};
 #pragma unroll
                 for (int k = 0; k < 3; k++) {
-                    if (!(fabs(v[k]) < 9.0e18)) continue;
+                    // outside the range the scene's bound guarantees (rtc_api.cu accumulator_scale: e.g. a NaN out of
+                    // a degenerate normal): the frame is flagged, never silently wrong
+                    if (!(fabs(v[k]) < 9.0e18)) {
+                        err |= ERR_ACC_RANGE;
+                        continue;
+                    }
                     long long a = __double_as_longlong(PK(PK_PCOL + k)) + __double2ll_rn(v[k]);
                     PK(PK_PCOL + k) = __longlong_as_double(a);
                 }

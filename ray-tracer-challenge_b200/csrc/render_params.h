@@ -128,5 +128,11 @@ int launch_render_mesh(const DScene& S, const RenderParams& P, int lpp, int grid
 int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
 int occupancy_render_mesh(int* blocks_per_sm, size_t smem);
 int occupancy_render_analytic(int* blocks_per_sm, size_t smem);
+// render_mesh_lean.cu / render_analytic_lean.cu: render_kernel<MESH, LPP, LEAN = true> for scenes without CSG objects,
+// guard boxes and non-solid patterns
+int launch_render_mesh_lean(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
+int launch_render_analytic_lean(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
+int occupancy_render_mesh_lean(int* blocks_per_sm, size_t smem);
+int occupancy_render_analytic_lean(int* blocks_per_sm, size_t smem);
 
 }  // namespace rtc

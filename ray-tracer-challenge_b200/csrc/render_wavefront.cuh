@@ -34,7 +34,7 @@ namespace rtc {
 template <bool MESH>
 __device__ __forceinline__ void wf_trace(Query& q, const DScene& S, int* stack, int* err, bool live) {
     MeshTrav trav;
-    bool busy = trace_begin<MESH>(q, S, trav, err, live);
+    bool busy = trace_begin<MESH, false>(q, S, trav, err, live);
     if constexpr (MESH) {
         while (__any_sync(0xffffffffu, busy)) {
             if (busy) busy = mesh_inner(q, S, trav, stack, err);
@@ -46,11 +46,14 @@ __device__ __forceinline__ void wf_trace(Query& q, const DScene& S, int* stack, 
 }
 
 // weight x colour added to a pixel: exact integer addition
-__device__ __forceinline__ void wf_add(long long* acc, int pix, V3 c, double scale) {
+__device__ __forceinline__ void wf_add(long long* acc, int pix, V3 c, double scale, int* err) {
     double v[3] = {c.x * scale, c.y * scale, c.z * scale};
 #pragma unroll
     for (int k = 0; k < 3; k++) {
-        if (!(fabs(v[k]) < 9.0e18)) continue;  // non-finite or out of range: dropped (cannot occur within the bound)
+        if (!(fabs(v[k]) < 9.0e18)) {  // non-finite or beyond the scene's bound: the frame is flagged (ERR_ACC_RANGE)
+            *err |= ERR_ACC_RANGE;
+            continue;
+        }
         long long i = __double2ll_rn(v[k]);
         if (i) atomicAdd(reinterpret_cast<unsigned long long*>(acc + 3ll * pix + k), (unsigned long long)i);
     }
@@ -195,7 +198,7 @@ wave_kernel(DScene S, WaveParams W) {
             q.t = RTC_INF;
             q.leaf = -1;
             q.a = q.b = 0.0;
-            q.c_leaf = -1;
+            q.c_leaf = 0;  // Q_CLOSEST: q.a / q.b hold the u,v of the hit triangle
             q.flag = 0;
             wf_trace<MESH>(q, S, stack, &err, live);
 
@@ -216,8 +219,8 @@ wave_kernel(DScene S, WaveParams W) {
                 const double* nrm = nullptr;
                 if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
                     nrm = S.normals[L.triangle].n;
-                    if (kind == RTC_SMOOTH_TRIANGLE) {
-                        // u,v of a triangle found outside the mesh path: same ray, same test, same values
+                    if (kind == RTC_SMOOTH_TRIANGLE && !q.c_leaf) {
+                        // u,v of a smooth triangle that is a CSG operand: same ray, same test, same values
                         const rtc_triangle& T = S.blob_tris[L.triangle];
                         double tt;
                         tri_intersect(v3(T.p1[0], T.p1[1], T.p1[2]), v3(T.e1[0], T.e1[1], T.e1[2]),
@@ -348,7 +351,7 @@ wave_kernel(DScene S, WaveParams W) {
             double2 a = p[0], b = p[1], c = p[2], e = p[3], f = p[4], g = p[5], h = p[6];
             const V3 over = v3(a.x, a.y, b.x), normal = v3(b.y, c.x, c.y), rd = v3(e.x, e.y, f.x), color = v3(f.y, g.x, g.y);
             V3 sum = wf_light<MESH>(S, over, normal, rd, color, __double2loint(h.y), li, live, stack, &err, n_culled);
-            if (live) wf_add(W.acc, __double2hiint(h.y), sum * h.x, W.scale);
+            if (live) wf_add(W.acc, __double2hiint(h.y), sum * h.x, W.scale, &err);
         }
     }
 

@@ -1,6 +1,7 @@
 // Device-side f64 vector helpers and the per-leaf closed-form intersection / normal routines.
-// Each routine cites the reference function it computes the same values as; arithmetic order
-// follows the reference except that nvcc contracts a*b+c into DFMA (differences ~1e-16 relative).
+// Each routine cites the reference function it computes the same values as, in the reference's operation
+// order; the library is compiled with -fmad=false (Makefile), so a*b+c stays an IEEE multiply and an IEEE add as
+// in the Zig build and the results are bit-identical to the oracle's.
 #pragma once
 #include <cuda_runtime.h>
 

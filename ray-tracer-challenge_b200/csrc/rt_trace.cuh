@@ -20,11 +20,11 @@ namespace rtc {
 #define RTC_CSG_SEG 16
 
 enum { Q_CLOSEST = 0, Q_SHADOW = 1, Q_CONTAINERS = 2 };
-enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8, ERR_QUEUE = 16 };
+enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8, ERR_QUEUE = 16, ERR_ACC_RANGE = 32 };
 
 // One world query.  The three modes never coexist, so they share their fields:
 //                 t                 leaf        a       b            c_leaf      flag
-//   Q_CLOSEST     best t so far     best leaf   u       v            -           -
+//   Q_CLOSEST     best t so far     best leaf   u       v            u,v valid   -
 //   Q_SHADOW      light distance    -           -       -            -           shadowed
 //   Q_CONTAINERS  t of the hit      hit leaf    c_t     hit_last_t   c_leaf      hit_odd
 // In every mode nothing beyond t can change the result: t is the far end of the useful range.
@@ -131,6 +131,7 @@ __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint
             if (t >= 0.0 && (t < q.t || (t == q.t && leaf < q.leaf))) {
                 q.t = t;
                 q.leaf = leaf;
+                q.c_leaf = 0;  // not a triangle whose u,v are in q.a / q.b (trace_prim sets it for a stray triangle)
             }
         }
     } else if (q.mode == Q_SHADOW) {
@@ -163,54 +164,73 @@ __device__ __forceinline__ unsigned prim_mask(const Query& q, const DScene& S, c
     return mask;
 }
 
+// LEAN (rtc_api.cu lean_scene): no guards and no stray triangles among the prims.
+template <bool LEAN>
 __device__ __forceinline__ void trace_prim(Query& q, const DScene& S, int i) {
     int leaf_id = S.prims[i].leaf;
     uint32_t flags = S.prims[i].flags;
     const rtc_leaf& L = S.leaves[leaf_id];
-    for (int g = L.guard; g >= 0;) {  // group.zig:46-50 for boxes that are not supersets
-        const rtc_guard& G = S.guards[g];
-        double a, b;
-        if (!ref_slabs(q.o, q.d, G.bmin, G.bmax, a, b)) return;
-        g = G.next;
+    if constexpr (!LEAN) {
+        for (int g = L.guard; g >= 0;) {  // group.zig:46-50 for boxes that are not supersets
+            const rtc_guard& G = S.guards[g];
+            double a, b;
+            if (!ref_slabs(q.o, q.d, G.bmin, G.bmax, a, b)) return;
+            g = G.next;
+        }
     }
     M34 inv = load_m34(S.transforms[L.transform].inverse);
     V3 oo = xf_point(inv, q.o), dd = xf_vec(inv, q.d);  // ray.zig:30-32
     double ts[4];
     int n;
     int kind = L.kind;
-    if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
+    if (!LEAN && (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE)) {
         const rtc_triangle& T = S.blob_tris[L.triangle];
         double u, v;
         n = tri_intersect(v3(T.p1[0], T.p1[1], T.p1[2]), v3(T.e1[0], T.e1[1], T.e1[2]), v3(T.e2[0], T.e2[1], T.e2[2]),
                           oo, dd, ts[0], u, v)
                 ? 1
                 : 0;
-    } else {
-        n = leaf_intersect(kind, flags, L.minimum, L.maximum, oo, dd, ts);
+        const double t_before = q.t;
+        const int leaf_before = q.leaf;
+        accept(q, S, leaf_id, flags, n, ts);
+        if (q.mode == Q_CLOSEST && (q.t != t_before || q.leaf != leaf_before)) {  // this triangle is the new closest hit
+            q.a = u;
+            q.b = v;
+            q.c_leaf = 1;
+        }
+        return;
     }
+    n = leaf_intersect(kind, flags, L.minimum, L.maximum, oo, dd, ts);
     accept(q, S, leaf_id, flags, n, ts);
 }
 
 // ---- meshes ---------------------------------------------------------------------------------------
 __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, int count, V3 oo, V3 dd,
-                                          uint32_t flags) {
+                                          const int32_t* __restrict__ lmap) {
     for (int i = 0; i < count; i++) {
         const double* p = reinterpret_cast<const double*>(S.tris + first + i);
         double2 a = ld2(p), b = ld2(p + 2), c = ld2(p + 4), e = ld2(p + 6), f = ld2(p + 8);
         double t, u, v;
+        // (deciding u < 0, u > 1, v < 0, u + v > 1 on the undivided quantities first, with margins inside which the
+        // reference's own operations decide, was measured on B200: dragons 0.871 ms against 0.849 with the plain test
+        // -- the division is not what the time goes into; profiles/README.md)
         if (!tri_intersect(v3(a.x, a.y, b.x), v3(b.y, c.x, c.y), v3(e.x, e.y, f.x), oo, dd, t, u, v)) continue;
-        int leaf = (int)(__double_as_longlong(f.y) & 0xffffffffLL);
+        const int rank = (int)(__double_as_longlong(f.y) & 0xffffffffLL);  // DTri.leaf: rank in the geometry
         if (q.mode == Q_CLOSEST) {
-            if (t >= 0.0 && (t < q.t || (t == q.t && leaf < q.leaf))) {
-                q.t = t;
-                q.leaf = leaf;
-                q.a = u;
-                q.b = v;
+            if (t >= 0.0 && t <= q.t) {
+                const int leaf = __ldg(lmap + rank);  // the instance's rtc_leaf: read only for a candidate
+                if (t < q.t || leaf < q.leaf) {
+                    q.t = t;
+                    q.leaf = leaf;
+                    q.a = u;
+                    q.b = v;
+                    q.c_leaf = 1;  // u,v valid
+                }
             }
         } else if (q.mode == Q_SHADOW) {
             if (t >= 0.0 && t < q.t) q.flag = 1;
         } else {
-            cont_add(q, leaf, 1, &t);
+            cont_add(q, __ldg(lmap + rank), 1, &t);
         }
     }
 }
@@ -225,6 +245,7 @@ struct MeshTrav {
     int mbase;      // meshes [mbase, mbase + 32) are described by mask
     unsigned mask;  // candidate meshes not visited yet
     int node, sp;
+    int lmap;       // DMesh.leaf_map of the mesh being traversed
     float t_hi;
     V3 oo, dd;  // the ray in the current mesh's object space
     FRay r;
@@ -282,6 +303,7 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
             M34 inv = load_m34(S.transforms[M.transform].inverse);
             T.oo = xf_point(inv, q.o), T.dd = xf_vec(inv, q.d);
             T.r = make_fray(T.oo, T.dd, M.bound_abs[0], M.bound_abs[1], M.bound_abs[2]);
+            T.lmap = M.leaf_map;
             float tn;
             if (!fbox(T.r, M.lo[0], M.lo[1], M.lo[2], M.hi[0], M.hi[1], M.hi[2], t_lo, T.t_hi, tn)) continue;
             node = M.root;
@@ -325,7 +347,7 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
 
 __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T, int* stack) {
     int enc = ~T.node;
-    mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, 0);
+    mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, S.mesh_leaf + T.lmap);
     if (q.mode == Q_SHADOW && q.flag) return false;
     if (q.mode == Q_CLOSEST) T.t_hi = __double2float_ru(q.t);
     if (T.sp > 0) {
@@ -435,6 +457,7 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
                 if (ts[i] < q.t || (ts[i] == q.t && ids[i] < q.leaf)) {
                     q.t = ts[i];
                     q.leaf = ids[i];
+                    q.c_leaf = 0;  // a CSG operand: u,v of a smooth triangle are recomputed by the caller
                 }
                 break;
             }
@@ -465,7 +488,7 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
 // Prims: each lane's candidate mask is OR-reduced over the warp and the warp steps through the union
 // in prim order -- prims no lane can reach cost nothing, and at every step the participating lanes
 // run the SAME prim (same kind: no divergence inside the intersection switch).
-template <bool MESH>
+template <bool MESH, bool LEAN>
 __device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav& T, int* err, bool live) {
     FRay wr = make_fray(q.o, q.d, S.world_abs[0], S.world_abs[1], S.world_abs[2]);
     for (int base = 0; base < S.n_prims; base += 32) {
@@ -474,13 +497,15 @@ __device__ __forceinline__ bool trace_begin(Query& q, const DScene& S, MeshTrav&
         while (todo) {
             int i = __ffs(todo) - 1;
             todo &= todo - 1;
-            if (((mine >> i) & 1u) && !(q.mode == Q_SHADOW && q.flag)) trace_prim(q, S, base + i);
+            if (((mine >> i) & 1u) && !(q.mode == Q_SHADOW && q.flag)) trace_prim<LEAN>(q, S, base + i);
         }
     }
     if (!live) return false;
-    for (int i = 0; i < S.n_csg; i++) {
-        if (q.mode == Q_SHADOW && q.flag) return false;
-        trace_csg(q, S, S.csg_roots[i], err);
+    if constexpr (!LEAN) {
+        for (int i = 0; i < S.n_csg; i++) {
+            if (q.mode == Q_SHADOW && q.flag) return false;
+            trace_csg(q, S, S.csg_roots[i], err);
+        }
     }
     if constexpr (!MESH) return false;
     if (S.n_meshes == 0 || (q.mode == Q_SHADOW && q.flag)) return false;

@@ -53,6 +53,7 @@ struct rtc_scene {
     long long* wf_acc = nullptr;
     unsigned long long* wf_counters = nullptr;
     bool has_secondary = false;  // some material is reflective or transparent: rays beyond level 0 can exist
+    bool lean = false;           // no CSG, no guard boxes, solid patterns only: render_kernel<MESH, LPP, LEAN = true>
     // Which of the two kernels renders this scene faster is MEASURED (the answer depends on the scene: the
     // wavefront wins where pixels have long or branching ray trees, the megakernel where they do not and on
     // small frames): frames 1-4 alternate between the heuristic choice and the other kernel, later frames use the faster one.
@@ -67,6 +68,13 @@ struct rtc_scene {
     size_t tile_cap = 0;      // tiles the two arrays hold
     size_t order_tiles = 0;   // tiles the current permutation covers (0: none yet)
 };
+
+static int launch_mega(const rtc_scene* s, const RenderParams& P, int lpp, cudaStream_t stream) {
+    if (s->d.n_meshes > 0)
+        return s->lean ? launch_render_mesh_lean(s->d, P, lpp, s->grid, s->smem, stream) : launch_render_mesh(s->d, P, lpp, s->grid, s->smem, stream);
+    return s->lean ? launch_render_analytic_lean(s->d, P, lpp, s->grid, s->smem, stream)
+                   : launch_render_analytic(s->d, P, lpp, s->grid, s->smem, stream);
+}
 
 // RTC_KERNEL=mega|wave pins the kernel; default (auto) measures both on the first four frames of a scene.
 static int forced_kernel() {  // read at every render: tests switch it between frames
@@ -148,6 +156,55 @@ void rtc_scene_destroy(rtc_scene* s) {
     delete s;
 }
 
+// Host arrays of a scene -> one staging buffer with 256-byte aligned sections (uploaded with ONE copy); the offsets
+// of the sections are what DScene's pointers are made of.
+struct SlabLayout {
+    size_t lights, materials, patterns, uvs, images, texels, transforms, leaves, normals, blob_tris, guards, nodes, prims, meshes,
+        bvh, tris, csg_prog, csg_roots, mesh_leaf;
+};
+static SlabLayout stage_slab(const HostScene& hs, std::vector<uint8_t>& stage) {
+    auto put = [&](const void* p, size_t bytes) -> size_t {
+        size_t off = (stage.size() + 255) & ~size_t(255);
+        stage.resize(off + bytes);
+        if (bytes) std::memcpy(&stage[off], p, bytes);
+        return off;
+    };
+#define PUT(vec) put((vec).data(), (vec).size() * sizeof((vec)[0]))
+    SlabLayout o;
+    o.lights = PUT(hs.lights), o.materials = PUT(hs.materials), o.patterns = PUT(hs.patterns), o.uvs = PUT(hs.uvs);
+    o.images = PUT(hs.images), o.texels = PUT(hs.texels), o.transforms = PUT(hs.transforms), o.leaves = PUT(hs.leaves);
+    o.normals = PUT(hs.normals), o.blob_tris = PUT(hs.blob_tris), o.guards = PUT(hs.guards), o.nodes = PUT(hs.nodes);
+    o.prims = PUT(hs.prims), o.meshes = PUT(hs.meshes), o.bvh = PUT(hs.bvh), o.tris = PUT(hs.tris);
+    o.csg_prog = PUT(hs.csg_prog), o.csg_roots = PUT(hs.csg_roots), o.mesh_leaf = PUT(hs.mesh_leaf);
+#undef PUT
+    return o;
+}
+
+int rtc_blob_inspect(const void* blob, size_t nbytes, rtc_scene_info* info) {
+    if (!info) return fail(RTC_ERR_INVALID, "rtc_blob_inspect: info_out is NULL");
+    std::memset(info, 0, sizeof *info);
+    HostScene hs;
+    auto t0 = std::chrono::steady_clock::now();
+    try {
+        build_host_scene(blob, nbytes, hs);
+    } catch (const std::exception& e) {
+        return fail(RTC_ERR_INVALID, e.what());
+    }
+    std::vector<uint8_t> stage;
+    stage_slab(hs, stage);
+    info->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    info->n_prims = (uint32_t)hs.prims.size();
+    info->n_meshes = (uint32_t)hs.meshes.size();
+    info->n_geometries = (uint32_t)hs.n_geometries;
+    info->n_csg = (uint32_t)hs.csg_roots.size();
+    info->n_bvh_nodes = hs.bvh.size();
+    info->n_mesh_triangles = hs.tris.size();
+    info->device_bytes = stage.size() + 256;
+    info->bvh_max_depth = (uint32_t)hs.bvh_max_depth;
+    info->n_leaves = (uint32_t)hs.leaves.size();
+    return RTC_OK;
+}
+
 int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if (!out) return fail(RTC_ERR_INVALID, "rtc_scene_create: out is NULL");
     *out = nullptr;
@@ -170,19 +227,7 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     }
     // ---- one slab, 256-byte aligned sections, one H2D copy --------------------------------------
     std::vector<uint8_t> stage;
-    auto put = [&](const void* p, size_t bytes) -> size_t {
-        size_t off = (stage.size() + 255) & ~size_t(255);
-        stage.resize(off + bytes);
-        if (bytes) std::memcpy(&stage[off], p, bytes);
-        return off;
-    };
-#define PUT(vec) put((vec).data(), (vec).size() * sizeof((vec)[0]))
-    size_t o_lights = PUT(hs.lights), o_mat = PUT(hs.materials), o_pat = PUT(hs.patterns), o_uv = PUT(hs.uvs);
-    size_t o_img = PUT(hs.images), o_tex = PUT(hs.texels), o_xf = PUT(hs.transforms), o_leaf = PUT(hs.leaves);
-    size_t o_nrm = PUT(hs.normals), o_btri = PUT(hs.blob_tris), o_guard = PUT(hs.guards), o_node = PUT(hs.nodes);
-    size_t o_prim = PUT(hs.prims), o_mesh = PUT(hs.meshes), o_bvh = PUT(hs.bvh), o_tri = PUT(hs.tris);
-    size_t o_prog = PUT(hs.csg_prog), o_root = PUT(hs.csg_roots);
-#undef PUT
+    const SlabLayout o = stage_slab(hs, stage);
     s->slab_bytes = stage.size() + 256;
     auto bail = [&](cudaError_t err, const char* what) {
         std::string msg = std::string(what) + ": " + cudaGetErrorString(err);
@@ -197,24 +242,25 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
     const uint8_t* b = static_cast<const uint8_t*>(s->slab);
     DScene& d = s->d;
-    d.lights = (const rtc_light*)(b + o_lights);
-    d.materials = (const rtc_material*)(b + o_mat);
-    d.patterns = (const rtc_pattern*)(b + o_pat);
-    d.uvs = (const rtc_uv_pattern*)(b + o_uv);
-    d.images = (const rtc_image*)(b + o_img);
-    d.texels = b + o_tex;
-    d.transforms = (const rtc_transform*)(b + o_xf);
-    d.leaves = (const rtc_leaf*)(b + o_leaf);
-    d.normals = (const rtc_tri_normals*)(b + o_nrm);
-    d.blob_tris = (const rtc_triangle*)(b + o_btri);
-    d.guards = (const rtc_guard*)(b + o_guard);
-    d.nodes = (const rtc_node*)(b + o_node);
-    d.prims = (const DPrim*)(b + o_prim);
-    d.meshes = (const DMesh*)(b + o_mesh);
-    d.bvh = (const BvhNode*)(b + o_bvh);
-    d.tris = (const DTri*)(b + o_tri);
-    d.csg_prog = (const int4*)(b + o_prog);
-    d.csg_roots = (const DCsgRoot*)(b + o_root);
+    d.lights = (const rtc_light*)(b + o.lights);
+    d.materials = (const rtc_material*)(b + o.materials);
+    d.patterns = (const rtc_pattern*)(b + o.patterns);
+    d.uvs = (const rtc_uv_pattern*)(b + o.uvs);
+    d.images = (const rtc_image*)(b + o.images);
+    d.texels = b + o.texels;
+    d.transforms = (const rtc_transform*)(b + o.transforms);
+    d.leaves = (const rtc_leaf*)(b + o.leaves);
+    d.normals = (const rtc_tri_normals*)(b + o.normals);
+    d.blob_tris = (const rtc_triangle*)(b + o.blob_tris);
+    d.guards = (const rtc_guard*)(b + o.guards);
+    d.nodes = (const rtc_node*)(b + o.nodes);
+    d.prims = (const DPrim*)(b + o.prims);
+    d.meshes = (const DMesh*)(b + o.meshes);
+    d.bvh = (const BvhNode*)(b + o.bvh);
+    d.tris = (const DTri*)(b + o.tris);
+    d.mesh_leaf = (const int32_t*)(b + o.mesh_leaf);
+    d.csg_prog = (const int4*)(b + o.csg_prog);
+    d.csg_roots = (const DCsgRoot*)(b + o.csg_roots);
     d.n_lights = (int32_t)hs.lights.size();
     d.n_prims = (int32_t)hs.prims.size();
     d.n_meshes = (int32_t)hs.meshes.size();
@@ -231,7 +277,15 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     // parked per-lane state (render_kernel.cuh PK_SLOTS doubles per thread) + the BVH traversal stacks
     s->smem = (size_t)RTC_PARK_SLOTS * RTC_BLOCK_THREADS * sizeof(double) +
               (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
-    e = (cudaError_t)(d.n_meshes > 0 ? occupancy_render_mesh(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, s->smem));
+    {
+        // RTC_LEAN=0 keeps the general instantiation (tests compare the two)
+        const char* le = std::getenv("RTC_LEAN");
+        s->lean = !(le && le[0] == '0') && hs.csg_roots.empty() && hs.guards.empty();
+        for (const rtc_material& m : hs.materials)
+            if (hs.patterns[(size_t)m.pattern].kind != RTC_PAT_SOLID) s->lean = false;
+    }
+    if (d.n_meshes > 0) e = (cudaError_t)(s->lean ? occupancy_render_mesh_lean(&per_sm, s->smem) : occupancy_render_mesh(&per_sm, s->smem));
+    else e = (cudaError_t)(s->lean ? occupancy_render_analytic_lean(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, s->smem));
     if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;
@@ -363,10 +417,10 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
         stats->shadow_rays_culled = c[WC_CULLED];
     }
     if (c[WC_ERR]) {
-        char buf[160];
+        char buf[224];
         std::snprintf(buf, sizeof buf,
                       "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
-                      "4=CSG list, 8=BVH stack)",
+                      "4=CSG list, 8=BVH stack, 32=pixel sum out of the accumulator's range)",
                       c[WC_ERR]);
         return fail(RTC_ERR_CAPACITY, buf);
     }
@@ -510,8 +564,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     // of dragons.json 1080p without an order, 0.49 -> 0.39 ms.
     if (lpp == 0 && !P.tile_order) lpp = 2;
     P.n_items *= (unsigned long long)(lpp ? lpp : 1);
-    CUDA_TRY((cudaError_t)(s->d.n_meshes > 0 ? launch_render_mesh(s->d, P, lpp, s->grid, s->smem, stream)
-                                             : launch_render_analytic(s->d, P, lpp, s->grid, s->smem, stream)));
+    CUDA_TRY((cudaError_t)launch_mega(s, P, lpp, stream));
     CUDA_TRY(cudaEventRecord(s->ev1, stream));
     unsigned long long c[8];
     CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, stream));
@@ -539,10 +592,10 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     }
     if (s->best_ms[slot] < 0.0f || ms < s->best_ms[slot]) s->best_ms[slot] = ms;
     if (c[4]) {
-        char buf[160];
+        char buf[224];
         std::snprintf(buf, sizeof buf,
                       "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
-                      "4=CSG list, 8=BVH stack)",
+                      "4=CSG list, 8=BVH stack, 32=pixel sum out of the accumulator's range)",
                       c[4]);
         return fail(RTC_ERR_CAPACITY, buf);
     }

@@ -3,6 +3,8 @@
 #include "scene_build.hpp"
 
 #include <cmath>
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <future>
@@ -228,21 +230,38 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
     }
 
     // ---- top level: analytic prims, meshes ----------------------------------------------------------
-    std::map<std::pair<int32_t, uint32_t>, std::vector<DTri>> groups;
+    // A mesh INSTANCE = all non-CSG triangles sharing a world->object matrix and a casts_shadow flag.  Instances whose
+    // object-space triangles (positions, edges, normals, flat/smooth) are the same multiset share ONE geometry: one
+    // BVH, one DTri array (dragons.json: six instances of dragon.obj -> one 23,490-triangle geometry instead of six;
+    // the reference re-parses the file per instance, scene.zig:455-488).  What differs per instance -- matrix,
+    // material, and the ORDER of the leaves, which divide(8) derives from world-space boxes (group.zig:85-135) and
+    // which decides ties at equal t -- stays per instance: DTri.leaf is the triangle's rank in the geometry's
+    // canonical order and DMesh.leaf_map translates it into the instance's rtc_leaf index.
+    struct Instance {
+        int32_t transform;
+        uint32_t flags;
+        std::vector<int32_t> leaves;  // rtc_leaf indices, in leaf order
+        std::vector<int32_t> canon;   // the same leaves in canonical (content) order
+        uint64_t hash = 0;
+        int geometry = -1;
+    };
+    std::map<std::pair<int32_t, uint32_t>, size_t> inst_of;
+    std::vector<Instance> insts;
     for (size_t i = 0; i < hs.leaves.size(); i++) {
         if (in_csg[i]) continue;
         const rtc_leaf& l = hs.leaves[i];
         if (l.kind == RTC_TEST_SHAPE) continue;
         bool tri = l.kind == RTC_TRIANGLE || l.kind == RTC_SMOOTH_TRIANGLE;
         if (tri && l.guard < 0) {
-            const rtc_triangle& t = hs.blob_tris[(size_t)l.triangle];
-            DTri d;
-            std::memcpy(d.p1, t.p1, sizeof d.p1);
-            std::memcpy(d.e1, t.e1, sizeof d.e1);
-            std::memcpy(d.e2, t.e2, sizeof d.e2);
-            d.leaf = (int32_t)i;
-            d.pad = 0;
-            groups[{l.transform, l.flags & RTC_CASTS_SHADOW}].push_back(d);
+            auto key = std::make_pair(l.transform, l.flags & (uint32_t)RTC_CASTS_SHADOW);
+            auto it = inst_of.find(key);
+            if (it == inst_of.end()) {
+                it = inst_of.emplace(key, insts.size()).first;
+                insts.emplace_back();
+                insts.back().transform = key.first;
+                insts.back().flags = key.second;
+            }
+            insts[it->second].leaves.push_back((int32_t)i);
         } else {
             DPrim p{};
             p.leaf = (int32_t)i;
@@ -255,28 +274,92 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             hs.prims.push_back(p);
         }
     }
+    // content of a triangle as far as the kernels read it through DTri / rtc_tri_normals / rtc_leaf.kind
+    auto tri_cmp = [&](int32_t la, int32_t lb) {
+        const rtc_leaf &A = hs.leaves[(size_t)la], &B = hs.leaves[(size_t)lb];
+        int c = std::memcmp(hs.blob_tris[(size_t)A.triangle].p1, hs.blob_tris[(size_t)B.triangle].p1, 9 * sizeof(double));
+        if (c) return c;
+        c = std::memcmp(hs.normals[(size_t)A.triangle].n, hs.normals[(size_t)B.triangle].n, 9 * sizeof(double));
+        if (c) return c;
+        return A.kind < B.kind ? -1 : A.kind > B.kind ? 1 : 0;
+    };
+    static const bool no_instancing = [] {
+        const char* e = std::getenv("RTC_INSTANCING");
+        return e && e[0] == '0';
+    }();
+    // canonical order only where sharing is possible at all: another instance with the same triangle count
+    std::map<size_t, int> by_count;
+    for (const Instance& in : insts) by_count[in.leaves.size()]++;
+    {
+        std::vector<std::future<void>> jobs;
+        for (Instance& in : insts) {
+            in.canon = in.leaves;
+            if (no_instancing || by_count[in.leaves.size()] < 2) continue;
+            Instance* ip = &in;
+            jobs.push_back(std::async(std::launch::async, [ip, &tri_cmp, &hs] {
+                std::stable_sort(ip->canon.begin(), ip->canon.end(), [&](int32_t a, int32_t b) { return tri_cmp(a, b) < 0; });
+                uint64_t h = 1469598103934665603ull;  // FNV-1a over the triangle contents in canonical order
+                for (int32_t lf : ip->canon) {
+                    const rtc_leaf& L = hs.leaves[(size_t)lf];
+                    const unsigned char* p = reinterpret_cast<const unsigned char*>(hs.blob_tris[(size_t)L.triangle].p1);
+                    for (size_t k = 0; k < 9 * sizeof(double); k += 8) {
+                        uint64_t w;
+                        std::memcpy(&w, p + k, 8);
+                        h = (h ^ w) * 1099511628211ull;
+                    }
+                }
+                ip->hash = h;
+            }));
+        }
+        for (auto& j : jobs) j.get();
+    }
+    struct Geometry {
+        size_t first_inst;
+        int32_t root = 0;  // BvhNode index
+        float lo[3], hi[3];
+    };
+    std::vector<Geometry> geoms;
+    for (size_t i = 0; i < insts.size(); i++) {
+        Instance& in = insts[i];
+        if (!no_instancing && by_count[in.leaves.size()] >= 2) {
+            for (size_t g = 0; g < geoms.size() && in.geometry < 0; g++) {
+                const Instance& o = insts[geoms[g].first_inst];
+                if (o.hash != in.hash || o.canon.size() != in.canon.size()) continue;
+                bool same = true;
+                for (size_t k = 0; k < in.canon.size() && same; k++) same = tri_cmp(in.canon[k], o.canon[k]) == 0;
+                if (same) in.geometry = (int)g;
+            }
+        }
+        if (in.geometry < 0) {
+            in.geometry = (int)geoms.size();
+            geoms.push_back(Geometry{i});
+        }
+    }
     hs.bvh_max_depth = 0;
-    // the meshes are independent: one builder thread each (dragons.json: 6 x 23,490 triangles)
+    // the geometries are independent: one builder thread each
+    std::vector<std::vector<DTri>> gtris(geoms.size());
     std::vector<std::future<BvhBuild>> builds;
-    for (auto& kv : groups) {
-        const std::vector<DTri>* tris = &kv.second;
-        builds.push_back(std::async(groups.size() > 1 ? std::launch::async : std::launch::deferred,
+    for (size_t g = 0; g < geoms.size(); g++) {
+        const Instance& in = insts[geoms[g].first_inst];
+        std::vector<DTri>& v = gtris[g];
+        v.resize(in.canon.size());
+        for (size_t k = 0; k < in.canon.size(); k++) {
+            const rtc_triangle& t = hs.blob_tris[(size_t)hs.leaves[(size_t)in.canon[k]].triangle];
+            DTri& d = v[k];
+            std::memcpy(d.p1, t.p1, sizeof d.p1);
+            std::memcpy(d.e1, t.e1, sizeof d.e1);
+            std::memcpy(d.e2, t.e2, sizeof d.e2);
+            d.leaf = (int32_t)k;  // rank in the canonical order; DMesh.leaf_map makes it an rtc_leaf index
+            d.pad = 0;
+        }
+        const std::vector<DTri>* tris = &v;
+        builds.push_back(std::async(geoms.size() > 1 ? std::launch::async : std::launch::deferred,
                                     [tris] { return build_bvh(*tris); }));
     }
-    size_t build_i = 0;
-    for (auto& kv : groups) {
-        BvhBuild b = builds[build_i++].get();
-        DMesh m{};
-        m.transform = kv.first.first;
-        m.flags = kv.first.second;
-        m.root = (int32_t)hs.bvh.size();
-        m.n_tris = (int32_t)b.tris.size();
-        for (int a = 0; a < 3; a++) {
-            m.lo[a] = b.lo[a];
-            m.hi[a] = b.hi[a];
-            m.bound_abs[a] = std::fmax(std::fabs(b.lo[a]), std::fabs(b.hi[a]));
-        }
-        mesh_world_box(hs.transforms[(size_t)m.transform], m);
+    for (size_t g = 0; g < geoms.size(); g++) {
+        BvhBuild b = builds[g].get();
+        geoms[g].root = (int32_t)hs.bvh.size();
+        for (int a = 0; a < 3; a++) geoms[g].lo[a] = b.lo[a], geoms[g].hi[a] = b.hi[a];
         int32_t node_base = (int32_t)hs.bvh.size(), tri_base = (int32_t)hs.tris.size();
         for (BvhNode n : b.nodes) {
             // child references as the traversal holds them: inner node index >= 0, or a leaf as
@@ -288,8 +371,25 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             hs.bvh.push_back(n);
         }
         hs.tris.insert(hs.tris.end(), b.tris.begin(), b.tris.end());
-        hs.meshes.push_back(m);
         if (b.max_depth > hs.bvh_max_depth) hs.bvh_max_depth = b.max_depth;
+    }
+    hs.n_geometries = (int)geoms.size();
+    for (const Instance& in : insts) {
+        const Geometry& G = geoms[(size_t)in.geometry];
+        DMesh m{};
+        m.transform = in.transform;
+        m.flags = in.flags;
+        m.root = G.root;
+        m.n_tris = (int32_t)in.canon.size();
+        m.leaf_map = (int32_t)hs.mesh_leaf.size();
+        hs.mesh_leaf.insert(hs.mesh_leaf.end(), in.canon.begin(), in.canon.end());
+        for (int a = 0; a < 3; a++) {
+            m.lo[a] = G.lo[a];
+            m.hi[a] = G.hi[a];
+            m.bound_abs[a] = std::fmax(std::fabs(G.lo[a]), std::fabs(G.hi[a]));
+        }
+        mesh_world_box(hs.transforms[(size_t)m.transform], m);
+        hs.meshes.push_back(m);
     }
 
     // scale of the f32 slab-test error bound for the world-space pre-tests (rt_trace.cuh make_fray)

@@ -26,6 +26,8 @@ struct HostScene {
     std::vector<DMesh> meshes;
     std::vector<BvhNode> bvh;
     std::vector<DTri> tris;
+    std::vector<int32_t> mesh_leaf;  // DMesh.leaf_map tables, one after the other
+    int n_geometries = 0;            // distinct BVHs (<= meshes.size(): instances share them)
     std::vector<int4> csg_prog;
     std::vector<DCsgRoot> csg_roots;
     int bvh_max_depth = 0;
