@@ -45,7 +45,7 @@ typedef struct rtc_partition {
 typedef struct rtc_stats {
     uint64_t primary_rays, shadow_rays, secondary_rays; /* world.zig:91-92,160-165,178-187 */
     uint64_t pixels;
-    float kernel_ms; /* CUDA-event time of the render kernel(s) of this call */
+    float kernel_ms; /* CUDA-event time of the kernels of this call (render kernel + tile-order kernels, or the wavefront launches); replicated scenes: the slowest device */
     uint32_t kernel; /* which kernel rendered the frame: 0 megakernel, 1 wavefront, 2 megakernel with several lanes per pixel (small partitions) */
     uint64_t launches; /* kernels launched by this call */
     /* shadow rays (counted in shadow_rays, as the reference casts them) that were NOT traced because
@@ -55,8 +55,15 @@ typedef struct rtc_stats {
 
 const char* rtc_last_error(void);
 int rtc_device_count(void);
-/* Selects the CUDA device used by scenes created afterwards on this thread (default 0). */
+/* Selects the (first) CUDA device of scenes created afterwards (default 0; process-wide). */
 int rtc_set_device(int device);
+/* How many GPUs render a frame: scenes created afterwards are replicated on devices d .. d+n-1 (d = rtc_set_device).
+ * The blob is parsed and its BVHs built ONCE; the scene's slab is copied device to device.  A whole-frame render call on
+ * such a scene -- rtc_render, rtc_render_rgba8, rtc_render_device*, the lib.zig twin -- hands the interleaved 8-row
+ * tiles k, k+n, ... to device k and returns when all are in; frames are bit-identical to the one-device frame.  This is
+ * the knob that n_threads is in the reference (lib.zig:157-164 spawns n_threads workers; camera.zig:88-97 one task per
+ * row): the caller chooses how many workers, the library splits the rows.  Default 1. */
+int rtc_set_devices(int n);
 
 /* What rtc_scene_create builds out of a blob, without touching a device (host-side validation + mesh instancing +
  * BVH build only; runs anywhere): a World(f64) handed to Camera.render (world.zig:20-25) becomes n_prims analytic
@@ -101,6 +108,15 @@ int rtc_render_device(rtc_scene* scene, const rtc_camera* cam, int max_depth, co
  * pixels are independent, so the only exchange of the path is the framebuffer itself). */
 int rtc_render_device_frame(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                             double* d_frame, void* stream, rtc_stats* stats);
+/* rtc_render_device_frame without the wait: the frame is only put on `stream` (render kernel, tile-order kernels, a
+ * 64-byte copy of the ray counters), nothing is synchronised and no statistics are returned.  rtc_stats_fetch waits for
+ * the frames enqueued so far and hands out their statistics, oldest first (stats_out may be NULL to just drain; at most
+ * 16 frames are kept -- older ones are dropped); it returns the first error any of those frames raised.  The first
+ * four to six frames of a (scene, frame size) are measured to pick the kernel and therefore complete before the call
+ * returns.  Frames of one scene are ordered among themselves even when put on different streams. */
+int rtc_render_device_async(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
+                            double* d_frame, void* stream);
+int rtc_stats_fetch(rtc_scene* scene, rtc_stats* stats_out, uint32_t max_frames, uint32_t* n_out);
 uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part);
 
 /* Host loader: the C++ mirror of src/parsing (scene.zig:612, obj.zig:195) + flattener, for hosts

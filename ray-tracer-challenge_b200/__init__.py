@@ -65,7 +65,7 @@ class rtc_stats(ctypes.Structure):
 
 
 # every symbol include/rtc_b200.h declares
-EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
+EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_set_devices", "rtc_render_device_async", "rtc_stats_fetch", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
            "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png"]
 # include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
@@ -88,6 +88,9 @@ def lib():
     L.rtc_last_error.restype = cp
     L.rtc_device_count.restype = ctypes.c_int
     L.rtc_set_device.argtypes = [ctypes.c_int]
+    L.rtc_set_devices.argtypes = [ctypes.c_int]
+    L.rtc_render_device_async.argtypes = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, ctypes.POINTER(rtc_partition), vp, vp]
+    L.rtc_stats_fetch.argtypes = [vp, ctypes.POINTER(rtc_stats), ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint32)]
     L.rtc_blob_inspect.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(rtc_scene_info)]
     L.rtc_scene_create.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
     L.rtc_scene_destroy.argtypes = [vp]
@@ -224,16 +227,29 @@ class Canvas:
 
 
 class World:
-    """Device-resident world (world.zig:20-25 after flattening).  Owns the rtc_scene handle."""
+    """Device-resident world (world.zig:20-25 after flattening).  Owns the rtc_scene handle.
+    devices > 1: the scene is replicated on `devices` GPUs of this process (rtc_set_devices) and whole-frame renders use
+    all of them."""
 
-    def __init__(self, blob, device=0):
+    def __init__(self, blob, device=0, devices=1):
         L = lib()
         if L.rtc_device_count() <= 0:
             raise RtcError(RTC_ERR_CUDA, "no CUDA device visible; this renderer has no CPU fallback")
         _check(L.rtc_set_device(device))
+        _check(L.rtc_set_devices(devices))
         self._h = ctypes.c_void_p()
         self._blob_bytes = len(blob)
-        _check(L.rtc_scene_create(blob, len(blob), ctypes.byref(self._h)))
+        try:
+            _check(L.rtc_scene_create(blob, len(blob), ctypes.byref(self._h)))
+        finally:
+            L.rtc_set_devices(1)
+
+    def fetch_stats(self, max_frames=16):
+        """Waits for the frames put on a stream by Camera.render_device_async and returns their rtc_stats, oldest first."""
+        arr = (rtc_stats * max_frames)()
+        n = ctypes.c_uint32()
+        _check(lib().rtc_stats_fetch(self._h, arr, max_frames, ctypes.byref(n)))
+        return [arr[i] for i in range(n.value)]
 
     def close(self):
         if getattr(self, "_h", None):
@@ -315,6 +331,13 @@ class Camera:
         _check(lib().rtc_render_device_frame(world._h, ctypes.byref(self.c), max_depth, pref,
                                              ctypes.c_void_p(d_frame_ptr), ctypes.c_void_p(stream), ctypes.byref(st)))
         return st
+
+
+    def render_device_async(self, world, d_frame_ptr, max_depth=5, partition=None, stream=0):
+        """render_device_frame without the wait: the frame is put on `stream`; World.fetch_stats() collects the statistics."""
+        keep, pref = self._part(partition)
+        _check(lib().rtc_render_device_async(world._h, ctypes.byref(self.c), max_depth, pref,
+                                             ctypes.c_void_p(d_frame_ptr), ctypes.c_void_p(stream)))
 
 
 class SceneInfo:

@@ -53,9 +53,10 @@ enum {
     PK_N1 = 19,
     PK_N2 = 20,
     PK_T = 21,       // t of the current hit
+    PK_MB = 22,      // MB_SLOTS slots: the lane's mailbox for the work sharing of the mesh traversal (rt_trace.cuh trace_meshes)
     PK_SLOTS = RTC_PARK_SLOTS
 };
-static_assert(PK_T + 1 == PK_SLOTS, "RTC_PARK_SLOTS (render_params.h) out of date");
+static_assert(PK_MB + MB_SLOTS == PK_SLOTS, "RTC_PARK_SLOTS (render_params.h) out of date");
 __device__ __forceinline__ V3 pk_ld(const double* pk, int k) {
     return v3(pk[k * RTC_BLOCK], pk[(k + 1) * RTC_BLOCK], pk[(k + 2) * RTC_BLOCK]);
 }
@@ -297,13 +298,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
         busy = trace_begin<MESH, LEAN>(q, S, trav, &err, state != ST_IDLE && !skip);
         // every mesh through ONE warp-wide traversal loop; the full-mask votes are the points where
         // the warp reconverges, so inner-node steps and triangle tests each run with all traversing lanes
-        if constexpr (MESH) {
-            while (__any_sync(0xffffffffu, busy)) {
-                if (busy) busy = mesh_inner(q, S, trav, stack, &err);
-                if (!__any_sync(0xffffffffu, busy)) break;
-                if (busy) busy = mesh_leaf(q, S, trav, stack);
-            }
-        }
+        // (and lanes that are through help those that are not: trace_meshes)
+        if constexpr (MESH) trace_meshes(q, S, trav, stack, s_mem + PK_MB * RTC_BLOCK + (threadIdx.x & ~31u), &err, busy, state != ST_IDLE, lane);
 
 #ifdef RTC_TRIP_PROBE
         {   // how long does one warp trip through the world take? [6] max cycles, [7] trips | long trips << 32

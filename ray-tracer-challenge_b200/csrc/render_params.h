@@ -19,7 +19,8 @@ namespace rtc {
 #define RTC_TILE_W (1u << RTC_TILE_W_LOG2)
 #define RTC_TILE_H (1u << RTC_TILE_H_LOG2)
 
-#define RTC_PARK_SLOTS 22  // doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*)
+#define RTC_PARK_SLOTS 27  // doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*), mailbox included
+#define RTC_MAILBOX_SLOTS 5  // rt_trace.cuh MB_SLOTS (the wavefront kernels keep only these in shared memory)
 
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)
     unsigned long long hsize, vsize;

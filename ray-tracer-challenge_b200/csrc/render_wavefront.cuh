@@ -36,11 +36,9 @@ __device__ __forceinline__ void wf_trace(Query& q, const DScene& S, int* stack, 
     MeshTrav trav;
     bool busy = trace_begin<MESH, false>(q, S, trav, err, live);
     if constexpr (MESH) {
-        while (__any_sync(0xffffffffu, busy)) {
-            if (busy) busy = mesh_inner(q, S, trav, stack, err);
-            if (!__any_sync(0xffffffffu, busy)) break;
-            if (busy) busy = mesh_leaf(q, S, trav, stack);
-        }
+        // the mailboxes (MB_SLOTS doubles per thread) precede the stacks in dynamic shared memory
+        extern __shared__ double s_wf[];
+        trace_meshes(q, S, trav, stack, s_wf + (threadIdx.x & ~31u), err, busy, live, threadIdx.x & 31u);
     }
     (void)trav;
 }
@@ -131,8 +129,8 @@ __device__ __forceinline__ V3 wf_light(const DScene& S, V3 over, V3 normal, V3 r
 template <bool MESH>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_WF_BLOCKS_MESH : RTC_WF_BLOCKS_ANALYTIC)
 wave_kernel(DScene S, WaveParams W) {
-    extern __shared__ int s_stack[];  // MESH: S.stack_cap x RTC_BLOCK ints, column per thread
-    int* stack = s_stack + threadIdx.x;
+    extern __shared__ double s_wf[];  // MESH: MB_SLOTS x RTC_BLOCK doubles (mailboxes), then S.stack_cap x RTC_BLOCK ints, column per thread
+    int* stack = reinterpret_cast<int*>(s_wf + MB_SLOTS * RTC_BLOCK) + threadIdx.x;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     unsigned long long* C = W.counters;

@@ -245,6 +245,7 @@ struct MeshTrav {
     int mbase;      // meshes [mbase, mbase + 32) are described by mask
     unsigned mask;  // candidate meshes not visited yet
     int node, sp;
+    int sb;         // the lane's stack is [sb, sp): entries below sb were handed to other lanes (trace_meshes)
     int lmap;       // DMesh.leaf_map of the mesh being traversed
     float t_hi;
     V3 oo, dd;  // the ray in the current mesh's object space
@@ -273,6 +274,7 @@ __device__ __forceinline__ void mesh_begin(const Query& q, const DScene& S, cons
     T.mask = mesh_mask(q, S, wr, 0);
     T.node = RTC_MESH_END;
     T.sp = 0;
+    T.sb = 0;
     T.t_hi = query_t_hi(q);
 }
 
@@ -331,7 +333,7 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
                 node = c0;
             } else if (h1) {
                 node = c1;
-            } else if (sp > 0) {
+            } else if (sp > T.sb) {
                 sp--;
                 node = stack[sp * RTC_BLOCK];
             } else {
@@ -349,14 +351,210 @@ __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T
     int enc = ~T.node;
     mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, S.mesh_leaf + T.lmap);
     if (q.mode == Q_SHADOW && q.flag) return false;
-    if (q.mode == Q_CLOSEST) T.t_hi = __double2float_ru(q.t);
-    if (T.sp > 0) {
+    if (q.mode == Q_CLOSEST) T.t_hi = fminf(T.t_hi, __double2float_ru(q.t));  // (T.t_hi may hold a tighter bound found by a helper)
+    if (T.sp > T.sb) {
         T.sp--;
         T.node = stack[T.sp * RTC_BLOCK];
     } else {
         T.node = RTC_MESH_END;
     }
     return true;
+}
+
+// ---- the mesh traversal of one warp trip, with work sharing between the lanes ---------------------------------------
+// The lanes of a warp need very different numbers of steps for their queries (a ray that misses every mesh box needs
+// none, one that grazes a dragon hundreds), and the trip lasts as long as the slowest: measured on dragons.json, 10 of
+// 32 lanes were active per instruction of this loop.  So a lane that is through HELPS: at the point where the warp
+// reconverges anyway, idle lanes are matched (ballot + popc ranks) with lanes that still have pending subtrees on their
+// traversal stacks; the helper copies the donor's object-space ray by shuffles, takes the BOTTOM entry of the donor's
+// stack (the largest pending subtree) and walks it as a query of its own.  Results meet in per-lane "mailboxes" in
+// shared memory: closest hit = min over (t, leaf) -- associative, so the result is the same whoever finds what: exact;
+// shadow = any hit.  Bounds travel too: a hit found by anyone working for a query shrinks t_hi of all of them (one
+// shared-memory atomicMin per step), a shadow hit stops them.  Containers queries (parity of ALL hits) are not shared.
+// MEASURED on B200 (profiles/README.md, round 2): correct (frames and ray counts bit-identical, 70 GPU tests green) and
+// it does raise the lanes active per instruction of this loop (10.5 -> 14.1), but the frame gets SLOWER -- dragons.json
+// 1080p 0.87 -> 1.24 ms, teapot 0.66 -> 0.82, a 1/8 partition 0.27 -> 0.35 -- and stays slower when helping is made
+// rare (only shadow queries, only with >= 28 idle lanes and >= 2 pending entries: 1.14 ms): the warp executes MORE
+// instructions (578 M against 505 M: subtrees a closest-hit query would have culled, the bookkeeping at every step) and
+// the loop no longer fits the instruction cache (stall_no_instruction 1.0 -> 2.5 per issue; 52 bytes of spills).  This
+// kernel lives on a small, register-tight inner loop.  Off by default; -DRTC_STEAL=1 builds it.
+#ifndef RTC_STEAL
+#define RTC_STEAL 0
+#endif
+#ifndef RTC_STEAL_MIN_DEPTH
+#define RTC_STEAL_MIN_DEPTH 1  // pending entries a lane must have on its stack before it gives the bottom one away
+#endif
+#ifndef RTC_STEAL_MIN_IDLE
+#define RTC_STEAL_MIN_IDLE 1   // idle lanes a warp must have before any of them helps
+#endif
+#ifndef RTC_STEAL_MODES
+#define RTC_STEAL_MODES 3      // bit 0: shadow queries are shared, bit 1: closest-hit queries are shared
+#endif
+enum { MB_T = 0, MB_LF = 1, MB_U = 2, MB_V = 3, MB_BOUND = 4, MB_SLOTS = 5 };  // doubles per lane (stride RTC_BLOCK)
+#define RTC_UV_NONE 2  // Query::c_leaf of a helper that has not found anything yet
+
+// q, a finished Q_CLOSEST / Q_SHADOW task, merged into the mailbox of lane `tgt` (mbw = the warp's lane-0 column)
+__device__ __forceinline__ void mb_merge(double* mbw, int tgt, const Query& q) {
+    const double lf = mbw[MB_LF * RTC_BLOCK + tgt];  // hi word: flag, lo word: leaf
+    if (q.mode == Q_CLOSEST) {
+        if (q.leaf >= 0 && q.c_leaf != RTC_UV_NONE) {
+            const double mt = mbw[MB_T * RTC_BLOCK + tgt];
+            const int ml = __double2loint(lf);
+            if (ml < 0 || q.t < mt || (q.t == mt && q.leaf < ml)) {
+                mbw[MB_T * RTC_BLOCK + tgt] = q.t;
+                mbw[MB_LF * RTC_BLOCK + tgt] = __hiloint2double(q.c_leaf, q.leaf);
+                mbw[MB_U * RTC_BLOCK + tgt] = q.a;
+                mbw[MB_V * RTC_BLOCK + tgt] = q.b;
+            }
+        }
+    } else if (q.flag) {
+        mbw[MB_LF * RTC_BLOCK + tgt] = __hiloint2double(1, __double2loint(lf));
+    }
+}
+
+// Walks the meshes for the whole warp.  busy: this lane has mesh work set up in T (trace_begin).  own_live: q is a live
+// query of this lane (its result matters).  stack: this thread's column; mbw: the warp's lane-0 mailbox column.
+__device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, MeshTrav& T, int* stack, double* mbw, int* err,
+                                             bool busy, bool own_live, unsigned lane) {
+    const unsigned FULL = 0xffffffffu;
+#if RTC_STEAL
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int own_mode = q.mode;
+    const bool can_help = !(own_live && own_mode == Q_CONTAINERS);  // its four result fields do not fit a mailbox
+    bool shared = false;   // warp-uniform: mailboxes are in use in this trip
+    bool own_in_q = true;  // q still is this lane's OWN query
+    bool dirty = false;    // q holds a helper's task that is not in its owner's mailbox yet
+    int owner = (int)lane; // whose query the lane works on
+    // finished helpers put their results into their owners' mailboxes, one lane per mailbox at a time
+    auto flush = [&](bool want, int tgt) {
+        unsigned pending = __ballot_sync(FULL, want);
+        while (pending) {
+            const unsigned grp = __match_any_sync(FULL, want ? tgt : 32 + (int)lane);
+            if (want && (int)lane == __ffs(grp) - 1) {
+                mb_merge(mbw, tgt, q);
+                want = false;
+            }
+            __syncwarp();
+            pending = __ballot_sync(FULL, want);
+        }
+    };
+#endif
+    while (__any_sync(FULL, busy)) {
+        if (busy) busy = mesh_inner(q, S, T, stack, err);
+        bool at_leaf = busy;  // holding a leaf for mesh_leaf (a lane that takes over a subtree below holds an inner node)
+#if RTC_STEAL
+        const unsigned idle = __ballot_sync(FULL, !busy && can_help);
+        if (__popc(idle) >= RTC_STEAL_MIN_IDLE) {
+            bool can_give = false;
+            if (busy && (q.mode == Q_SHADOW ? (RTC_STEAL_MODES & 1) != 0 : q.mode == Q_CLOSEST && (RTC_STEAL_MODES & 2) != 0) &&
+                T.sp - T.sb >= RTC_STEAL_MIN_DEPTH)
+                can_give = stack[T.sb * RTC_BLOCK] >= 0;  // an inner node
+            const unsigned donors = __ballot_sync(FULL, can_give);
+            if (donors) {
+                if (!shared) {
+                    mbw[MB_T * RTC_BLOCK + lane] = RTC_INF;
+                    mbw[MB_LF * RTC_BLOCK + lane] = __hiloint2double(0, -1);
+                    reinterpret_cast<unsigned*>(mbw + MB_BOUND * RTC_BLOCK + lane)[0] = 0x7f800000u;  // +inf
+                    shared = true;
+                    __syncwarp();
+                }
+                const int n_d = __popc(donors), n_i = __popc(idle);
+                const int my_rank = __popc(idle & lt_mask);
+                const bool take = !busy && can_help && my_rank < n_d;
+                const bool give = can_give && __popc(donors & lt_mask) < n_i;
+                // what a taker holds goes to its mailbox first: its own finished query, or the task it helped with
+                flush(take && (own_in_q ? own_live : dirty), owner);
+                const int src = take ? (int)__fns(donors, 0, my_rank + 1) : (int)lane;
+                const int d_sb = __shfl_sync(FULL, T.sb, src);
+                const int d_owner = __shfl_sync(FULL, owner, src);
+                const int d_mode = __shfl_sync(FULL, q.mode, src);
+                const int d_leaf = __shfl_sync(FULL, q.leaf, src);
+                const int d_lmap = __shfl_sync(FULL, T.lmap, src);
+                const double d_t = __shfl_sync(FULL, q.t, src);
+                const float d_thi = __shfl_sync(FULL, T.t_hi, src);
+                const double ox = __shfl_sync(FULL, T.oo.x, src), oy = __shfl_sync(FULL, T.oo.y, src), oz = __shfl_sync(FULL, T.oo.z, src);
+                const double dx = __shfl_sync(FULL, T.dd.x, src), dy = __shfl_sync(FULL, T.dd.y, src), dz = __shfl_sync(FULL, T.dd.z, src);
+                FRay r;
+                r.ix = __shfl_sync(FULL, T.r.ix, src), r.iy = __shfl_sync(FULL, T.r.iy, src), r.iz = __shfl_sync(FULL, T.r.iz, src);
+                r.nx = __shfl_sync(FULL, T.r.nx, src), r.ny = __shfl_sync(FULL, T.r.ny, src), r.nz = __shfl_sync(FULL, T.r.nz, src);
+                r.fx = __shfl_sync(FULL, T.r.fx, src), r.fy = __shfl_sync(FULL, T.r.fy, src), r.fz = __shfl_sync(FULL, T.r.fz, src);
+                if (give) T.sb++;
+                __syncwarp();
+                if (take) {
+                    T.node = (stack - lane + src)[d_sb * RTC_BLOCK];
+                    T.sp = T.sb = 0;
+                    T.mask = 0;
+                    T.mbase = S.n_meshes;  // this subtree only: no further candidate meshes
+                    T.lmap = d_lmap;
+                    T.t_hi = d_thi;
+                    T.oo = v3(ox, oy, oz);
+                    T.dd = v3(dx, dy, dz);
+                    T.r = r;
+                    q.mode = d_mode;
+                    q.t = d_t;        // the bound (and, with the leaf, the tie-break) the donor has reached
+                    q.leaf = d_leaf;
+                    q.c_leaf = RTC_UV_NONE;
+                    q.flag = 0;
+                    owner = d_owner;
+                    own_in_q = false;
+                    dirty = true;
+                    busy = true;
+                    at_leaf = false;
+                }
+            }
+        }
+        if (shared) {
+            flush(!busy && dirty, owner);  // helpers that are through
+            if (!busy) dirty = false;
+            if (busy && q.mode == Q_CLOSEST) {  // the nearest hit anyone has found for this query bounds everyone's search
+                unsigned* bp = reinterpret_cast<unsigned*>(mbw + MB_BOUND * RTC_BLOCK + owner);
+                const unsigned mine = __float_as_uint(T.t_hi);  // t_hi >= 0: unsigned order is float order
+                const unsigned old = atomicMin(bp, mine);
+                T.t_hi = __uint_as_float(min(old, mine));
+            } else if (busy && q.mode == Q_SHADOW) {
+                if (__double2hiint(mbw[MB_LF * RTC_BLOCK + owner])) busy = false;  // someone found a hit: shadowed
+            }
+        }
+#endif
+        if (!__any_sync(FULL, busy)) break;
+        if (busy && at_leaf) busy = mesh_leaf(q, S, T, stack);
+    }
+#if RTC_STEAL
+    if (shared) {
+        flush(dirty, owner);
+        __syncwarp();
+        if (own_live) {
+            const double lf = mbw[MB_LF * RTC_BLOCK + lane];
+            const int ml = __double2loint(lf), mf = __double2hiint(lf);
+            if (own_mode == Q_CLOSEST) {
+                const double mt = mbw[MB_T * RTC_BLOCK + lane];
+                // own_in_q: the lane's own search result is still in q -- the better of the two; else the mailbox has all
+                const bool from_mb = !own_in_q || (ml >= 0 && (q.leaf < 0 || mt < q.t || (mt == q.t && ml < q.leaf)));
+                if (!own_in_q && ml < 0) {
+                    q.t = RTC_INF;
+                    q.leaf = -1;
+                    q.a = q.b = 0.0;
+                    q.c_leaf = 0;
+                } else if (from_mb) {
+                    q.t = mt;
+                    q.leaf = ml;
+                    q.c_leaf = mf;
+                    q.a = mbw[MB_U * RTC_BLOCK + lane];
+                    q.b = mbw[MB_V * RTC_BLOCK + lane];
+                }
+            } else if (own_mode == Q_SHADOW) {
+                if (!own_in_q) q.flag = mf;
+                else if (mf) q.flag = 1;
+            }
+            q.mode = own_mode;
+        }
+        __syncwarp();
+    }
+#else
+    (void)mbw;
+    (void)own_live;
+    (void)lane;
+#endif
 }
 
 // ---- CSG ------------------------------------------------------------------------------------------

@@ -16,9 +16,14 @@
 #include "scene_build.hpp"
 
 using namespace rtc;
+struct rtc_scene;
+
+#include <atomic>
 
 static thread_local std::string g_error;
-static thread_local int g_device = 0;
+// Process-wide (not per thread: the lib.zig twin creates its scene on a worker thread, rtc_renderer.cpp).
+static std::atomic<int> g_device{0};     // rtc_set_device: first device of scenes created afterwards
+static std::atomic<int> g_n_devices{1};  // rtc_set_devices: how many devices a scene is replicated on
 
 static int fail(int code, const std::string& msg) {
     g_error = msg;
@@ -39,7 +44,24 @@ struct rtc_scene {
     unsigned long long* d_counters = nullptr;  // 8 x u64
     double* d_frame = nullptr;                 // scratch framebuffer for the host-output entry points
     size_t d_frame_bytes = 0;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;  // wavefront path (synchronous)
+    // Frames in flight.  A render call only ENQUEUES work on its stream (counters memset, render kernel, the two tile
+    // order kernels, a 64-byte copy of the counters into pinned memory); the statistics of a frame are made out of
+    // its ring slot when somebody asks for them -- the synchronous entry points at once, rtc_stats_fetch later.
+    static constexpr int kRing = 16;
+    struct Frame {
+        int state = 0;  // 0 free, 1 on the stream, 2 statistics ready
+        int best_slot = 0, lpp = 1, rc = 0;
+        bool lpt = false;
+        uint64_t pixels = 0;
+        rtc_stats stats{};
+    };
+    Frame ring[kRing];
+    cudaEvent_t rev0[kRing] = {}, rev1[kRing] = {}, rev2[kRing] = {};  // kernel start / end, counters landed
+    unsigned long long* h_counters = nullptr;  // pinned, kRing x 8 u64
+    uint64_t seq_next = 0, seq_pop = 0;        // frames enqueued / handed out
+    cudaStream_t own_stream = nullptr;         // replicas (rtc_set_devices) render on a stream of their own
+    std::vector<rtc_scene*> replicas;          // the same scene on the other devices (primary only)
     int grid = 0;
     size_t smem = 0;  // dynamic shared memory per CTA: parked state + the BVH traversal stacks
     // wavefront path (render_wavefront.cuh): per-level queues, fixed-point accumulators, counters
@@ -126,6 +148,17 @@ int rtc_set_device(int device) {
     return RTC_OK;
 }
 
+int rtc_set_devices(int n) {
+    const int have = rtc_device_count();
+    if (n < 1 || g_device.load() + n > have) {
+        char buf[128];
+        std::snprintf(buf, sizeof buf, "rtc_set_devices(%d): devices %d..%d wanted, %d visible", n, g_device.load(), g_device.load() + n - 1, have);
+        return fail(RTC_ERR_CUDA, buf);
+    }
+    g_n_devices = n;
+    return RTC_OK;
+}
+
 uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part) {
     if (!part || part->n_parts <= 1) return vsize;
     uint64_t tr = part->tile_rows ? part->tile_rows : 1, rows = 0;
@@ -139,7 +172,10 @@ uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part) {
 
 void rtc_scene_destroy(rtc_scene* s) {
     if (!s) return;
+    for (rtc_scene* r : s->replicas) rtc_scene_destroy(r);
+    s->replicas.clear();
     cudaSetDevice(s->device);
+    cudaDeviceSynchronize();  // frames may still be on a stream
     if (s->slab) cudaFree(s->slab);
     if (s->d_counters) cudaFree(s->d_counters);
     if (s->d_tile_cost) cudaFree(s->d_tile_cost);
@@ -151,8 +187,15 @@ void rtc_scene_destroy(rtc_scene* s) {
     if (s->wf_acc) cudaFree(s->wf_acc);
     if (s->wf_counters) cudaFree(s->wf_counters);
     if (s->d_frame) cudaFree(s->d_frame);
+    if (s->h_counters) cudaFreeHost(s->h_counters);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    for (int i = 0; i < rtc_scene::kRing; i++) {
+        if (s->rev0[i]) cudaEventDestroy(s->rev0[i]);
+        if (s->rev1[i]) cudaEventDestroy(s->rev1[i]);
+        if (s->rev2[i]) cudaEventDestroy(s->rev2[i]);
+    }
+    if (s->own_stream) cudaStreamDestroy(s->own_stream);
     delete s;
 }
 
@@ -205,29 +248,17 @@ int rtc_blob_inspect(const void* blob, size_t nbytes, rtc_scene_info* info) {
     return RTC_OK;
 }
 
-int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
-    if (!out) return fail(RTC_ERR_INVALID, "rtc_scene_create: out is NULL");
-    *out = nullptr;
-    if (rtc_device_count() <= 0) return fail(RTC_ERR_CUDA, "rtc_scene_create: no CUDA device (there is no CPU fallback)");
-    HostScene hs;
-    try {
-        build_host_scene(blob, nbytes, hs);
-    } catch (const std::exception& e) {
-        return fail(RTC_ERR_INVALID, e.what());
-    }
-    if (hs.bvh_max_depth > 190) return fail(RTC_ERR_CAPACITY, "BVH deeper than the traversal stack can be made");
-    if (hs.csg_max_segments > 16) return fail(RTC_ERR_CAPACITY, "CSG nesting deeper than the segment stack");
-
+// The scene on ONE device.  src_slab != NULL: the slab is copied from that device's memory (peer copy over NVLink)
+// instead of from the host staging buffer.
+static int create_on_device(const HostScene& hs, const std::vector<uint8_t>& stage, const SlabLayout& o, int device,
+                            const void* src_slab, int src_device, rtc_scene** out) {
     rtc_scene* s = new rtc_scene();
-    s->device = g_device;
+    s->device = device;
     cudaError_t e = cudaSetDevice(s->device);
     if (e != cudaSuccess) {
         delete s;
         return fail(RTC_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
     }
-    // ---- one slab, 256-byte aligned sections, one H2D copy --------------------------------------
-    std::vector<uint8_t> stage;
-    const SlabLayout o = stage_slab(hs, stage);
     s->slab_bytes = stage.size() + 256;
     auto bail = [&](cudaError_t err, const char* what) {
         std::string msg = std::string(what) + ": " + cudaGetErrorString(err);
@@ -235,11 +266,20 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
         return fail(RTC_ERR_CUDA, msg);
     };
     if ((e = cudaMalloc(&s->slab, s->slab_bytes)) != cudaSuccess) return bail(e, "cudaMalloc(scene)");
-    if ((e = cudaMemcpy(s->slab, stage.data(), stage.size(), cudaMemcpyHostToDevice)) != cudaSuccess)
-        return bail(e, "cudaMemcpy(scene)");
+    // ---- one slab, 256-byte aligned sections, one copy -------------------------------------------
+    if (src_slab) e = cudaMemcpyPeer(s->slab, device, src_slab, src_device, stage.size());
+    else e = cudaMemcpy(s->slab, stage.data(), stage.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return bail(e, "cudaMemcpy(scene)");
     if ((e = cudaMalloc(&s->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail(e, "cudaMalloc(counters)");
+    if ((e = cudaHostAlloc(&s->h_counters, rtc_scene::kRing * 8 * sizeof(unsigned long long), cudaHostAllocDefault)) != cudaSuccess)
+        return bail(e, "cudaHostAlloc(counters)");
     if ((e = cudaEventCreate(&s->ev0)) != cudaSuccess) return bail(e, "cudaEventCreate");
     if ((e = cudaEventCreate(&s->ev1)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    for (int i = 0; i < rtc_scene::kRing; i++) {
+        if ((e = cudaEventCreate(&s->rev0[i])) != cudaSuccess) return bail(e, "cudaEventCreate");
+        if ((e = cudaEventCreate(&s->rev1[i])) != cudaSuccess) return bail(e, "cudaEventCreate");
+        if ((e = cudaEventCreateWithFlags(&s->rev2[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+    }
     const uint8_t* b = static_cast<const uint8_t*>(s->slab);
     DScene& d = s->d;
     d.lights = (const rtc_light*)(b + o.lights);
@@ -289,29 +329,34 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;
-    // wavefront kernels: no parked state, only the traversal stacks
-    s->wf_smem = (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
+    // wavefront kernels: no parked state, only the mailboxes and the traversal stacks
+    s->wf_smem = d.n_meshes > 0 ? (size_t)RTC_MAILBOX_SLOTS * RTC_BLOCK_THREADS * sizeof(double) + (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int) : 0;
     d.ri_all_one = 1;
+    double branch = 2.0;  // sum of the weights of a hit's children relative to its own: reflective + transparency
     for (const rtc_material& m : hs.materials) {
         if (m.reflective != 0.0 || m.transparency != 0.0) s->has_secondary = true;
         if (m.refractive_index != 1.0) d.ri_all_one = 0;
+        branch = std::fmax(branch, std::fabs(m.reflective) + std::fabs(m.transparency));
     }
     int wf_per_sm = 0;
     e = (cudaError_t)(d.n_meshes > 0 ? occupancy_wave_mesh(&wf_per_sm, s->wf_smem) : occupancy_wave_analytic(&wf_per_sm, s->wf_smem));
     if (e != cudaSuccess) return bail(e, "occupancy query (wavefront)");
     if (wf_per_sm < 1) wf_per_sm = 1;
     s->wf_grid = prop.multiProcessorCount * wf_per_sm;
-    // Fixed-point unit of the pixel accumulators: a pixel is a sum of at most 2^(depth+1) terms weight x lighting(),
-    // weight <= 1, |lighting()| <= sum over lights |I| x (ambient + diffuse + specular) x max |colour|.
+    // Fixed-point unit of the pixel accumulators: a pixel is the sum over the nodes of its ray tree of weight x lighting();
+    // the weights of level d add up to at most branch^d (branch = max over materials of reflective + transparency, at
+    // least 2: the JSON allows values above 1), levels 0..7; |lighting()| <= sum over lights |I| x (ambient + diffuse +
+    // specular) x max |colour|.  A term beyond the range (NaN included) sets ERR_ACC_RANGE instead of wrapping.
     {
-        double li = 0.0, coef = 1.0, col = 1.0;
+        double li = 0.0, coef = 1.0, col = 1.0, levels = 0.0, w = 1.0;
+        for (int lv = 0; lv <= 7; lv++, w *= branch) levels += w;
         for (const rtc_light& l : hs.lights)
             li += std::fmax(std::fabs(l.intensity[0]), std::fmax(std::fabs(l.intensity[1]), std::fabs(l.intensity[2])));
         for (const rtc_material& m : hs.materials)
             coef = std::fmax(coef, std::fabs(m.ambient) + std::fabs(m.diffuse) + std::fabs(m.specular));
         for (const rtc_pattern& pt : hs.patterns)
             for (int k = 0; k < 3; k++) col = std::fmax(col, std::fabs(pt.color[k]));
-        double bound = 256.0 * std::fmax(li, 1.0) * coef * col;
+        double bound = levels * std::fmax(li, 1.0) * coef * col;
         int ex = 0;
         if (!(bound < 1e300)) bound = 1e300;
         std::frexp(bound, &ex);          // bound < 2^ex
@@ -320,6 +365,55 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
         if (sh < -900) sh = -900;
         s->wf_scale = std::ldexp(1.0, sh);
     }
+    *out = s;
+    return RTC_OK;
+}
+
+int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
+    if (!out) return fail(RTC_ERR_INVALID, "rtc_scene_create: out is NULL");
+    *out = nullptr;
+    if (rtc_device_count() <= 0) return fail(RTC_ERR_CUDA, "rtc_scene_create: no CUDA device (there is no CPU fallback)");
+    HostScene hs;
+    try {
+        build_host_scene(blob, nbytes, hs);
+    } catch (const std::exception& e) {
+        return fail(RTC_ERR_INVALID, e.what());
+    }
+    if (hs.bvh_max_depth > 190) return fail(RTC_ERR_CAPACITY, "BVH deeper than the traversal stack can be made");
+    if (hs.csg_max_segments > 16) return fail(RTC_ERR_CAPACITY, "CSG nesting deeper than the segment stack");
+    std::vector<uint8_t> stage;
+    const SlabLayout o = stage_slab(hs, stage);
+    const int first = g_device.load(), n_dev = g_n_devices.load();
+    if (first + n_dev > rtc_device_count()) return fail(RTC_ERR_CUDA, "rtc_scene_create: fewer CUDA devices than rtc_set_devices asked for");
+    rtc_scene* s = nullptr;
+    int rc = create_on_device(hs, stage, o, first, nullptr, 0, &s);
+    if (rc) return rc;
+    // rtc_set_devices(n): the scene is parsed and built ONCE and its slab replicated device to device; every replica
+    // may store into device 0's memory (frames assembled there) -- camera.zig:88-97 hands one row to each of n_threads
+    // workers of ONE process, this hands interleaved row tiles to the n devices of one process.
+    for (int k = 1; k < n_dev; k++) {
+        rtc_scene* r = nullptr;
+        rc = create_on_device(hs, stage, o, first + k, s->slab, first, &r);
+        if (rc) {
+            rtc_scene_destroy(s);
+            return rc;
+        }
+        s->replicas.push_back(r);
+        cudaError_t e = cudaStreamCreateWithFlags(&r->own_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) {
+            e = cudaDeviceEnablePeerAccess(first, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+                e = cudaSuccess;
+            }
+        }
+        if (e != cudaSuccess) {
+            std::string msg = std::string("replica on device ") + std::to_string(first + k) + ": " + cudaGetErrorString(e);
+            rtc_scene_destroy(s);
+            return fail(RTC_ERR_CUDA, msg);
+        }
+    }
+    cudaSetDevice(first);
     *out = s;
     return RTC_OK;
 }
@@ -427,9 +521,54 @@ static int render_wavefront(rtc_scene* s, const RenderParams& P, cudaStream_t st
     return RTC_OK;
 }
 
-static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
-                         unsigned char* d_rgba, cudaStream_t stream, rtc_stats* stats, bool full_frame = false,
-                         bool spread_rows = false) {
+// ---- frames --------------------------------------------------------------------------------------------------------
+struct Target {              // where a frame goes
+    double* rgb = nullptr;   // device-addressable f64 canvas (device memory, peer memory or mapped host memory), or
+    unsigned char* rgba = nullptr;  // RGBA8
+    bool full_frame = false; // rows of the partition at their frame positions (else packed)
+    bool spread_rows = false;  // canvas in mapped host memory: strided row order, no cost order (see enqueue_frame)
+};
+
+// Makes the statistics of the frame in ring slot `slot` (waits for it if it is still on the stream).
+static int resolve_frame(rtc_scene* s, int slot) {
+    rtc_scene::Frame& f = s->ring[slot];
+    if (f.state != 1) return f.state == 2 ? f.rc : RTC_OK;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaEventSynchronize(s->rev2[slot]));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->rev0[slot], s->rev1[slot]));
+    const unsigned long long* c = s->h_counters + 8 * slot;
+#ifdef RTC_TRIP_PROBE
+    std::fprintf(stderr, "trip probe: max trip %.1f us, trips %llu, > 50 us: %llu, > 20 us: %llu (kernel %.3f ms)\n", c[6] / 1965.0,
+                 c[7] & 0xffffffffull, (c[7] >> 32) & 0xffffull, c[7] >> 48, ms);
+#endif
+    f.stats.primary_rays = c[1];
+    f.stats.shadow_rays = c[2];
+    f.stats.secondary_rays = c[3];
+    f.stats.pixels = f.pixels;
+    f.stats.kernel_ms = ms;  // render kernel + the two tile order kernels behind it
+    f.stats.launches = f.lpt ? 3 : 1;
+    f.stats.kernel = f.lpp != 1 ? 2u : 0u;
+    f.stats.shadow_rays_culled = c[5];
+    if (s->best_ms[f.best_slot] < 0.0f || ms < s->best_ms[f.best_slot]) s->best_ms[f.best_slot] = ms;
+    f.state = 2;
+    f.rc = RTC_OK;
+    if (c[4]) {
+        char buf[224];
+        std::snprintf(buf, sizeof buf,
+                      "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
+                      "4=CSG list, 8=BVH stack, 32=pixel sum out of the accumulator's range)",
+                      c[4]);
+        f.rc = fail(RTC_ERR_CAPACITY, buf);
+    }
+    return f.rc;
+}
+
+// Puts one frame (one partition on one device) on `stream`.  Returns the ring slot in *slot_out; with wait = true the
+// frame's statistics are ready on return (the wavefront path and the first frames of a scene, whose times pick the
+// kernel, always are).
+static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, const Target& tg,
+                         cudaStream_t stream, bool wait, int* slot_out) {
     if (!s || !cam) return fail(RTC_ERR_INVALID, "render: NULL scene or camera");
     if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
     if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
@@ -438,6 +577,20 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (part->n_parts == 0 || part->part >= part->n_parts || part->tile_rows == 0)
         return fail(RTC_ERR_INVALID, "render: bad partition");
     CUDA_TRY(cudaSetDevice(s->device));
+    // a free ring slot: the oldest frame nobody fetched is resolved (its time still counts for the kernel choice) and dropped
+    if (s->seq_next - s->seq_pop == (uint64_t)rtc_scene::kRing) {
+        const int old = (int)(s->seq_pop % rtc_scene::kRing);
+        resolve_frame(s, old);
+        s->ring[old].state = 0;
+        s->seq_pop++;
+    }
+    const int slot = (int)(s->seq_next % rtc_scene::kRing);
+    rtc_scene::Frame& F = s->ring[slot];
+    F = rtc_scene::Frame();
+    // The frames of a scene share its counters, tile costs and tile order: a frame put on ANOTHER stream than the one
+    // before it must still run behind it (and behind the order kernels that read its costs).
+    if (s->seq_next > 0) CUDA_TRY(cudaStreamWaitEvent(stream, s->rev2[(int)((s->seq_next - 1) % rtc_scene::kRing)], 0));
+
     RenderParams P{};
     P.cam.hsize = cam->hsize;
     P.cam.vsize = cam->vsize;
@@ -468,7 +621,7 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         P.row_group = (unsigned)(group > 0 ? group : 1);
         P.n_row_groups = n_tile_rows / P.row_group;
         unsigned st = 1;
-        if (forced >= 0 ? forced != 1 : spread_rows) {
+        if (forced >= 0 ? forced != 1 : tg.spread_rows) {
             st = forced > 1 ? (unsigned)forced : (unsigned)(0.381966 * P.n_row_groups);
             auto gcd = [](unsigned a, unsigned b) {
                 while (b) {
@@ -487,14 +640,19 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             P.n_row_groups = 0;
         }
     }
-    P.full_frame = full_frame ? 1 : 0;
+    P.full_frame = tg.full_frame ? 1 : 0;
     P.scale = s->wf_scale;
-    P.out = d_rgb;
-    P.out8 = d_rgba;
+    P.out = tg.rgb;
+    P.out8 = tg.rgba;
     P.counters = s->d_counters;
-    if (stats) std::memset(stats, 0, sizeof *stats);
-    if (P.rows == 0) return RTC_OK;
     const size_t n_px = (size_t)(P.rows * cam->hsize);
+    F.pixels = n_px;
+    if (P.rows == 0) {  // an empty partition: nothing to do, statistics all zero
+        F.state = 2;
+        s->seq_next++;
+        *slot_out = slot;
+        return RTC_OK;
+    }
     if (s->tuned_pixels != n_px) {  // another frame size (or partition): measure again
         s->tuned_pixels = n_px;
         s->frames = 0;
@@ -502,14 +660,17 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         s->order_tiles = 0;
     }
     int which = forced_kernel();
+    bool measuring = false;
     if (which < 0) {
         // first guess: the wavefront pays where rays recurse and the frame is big enough to amortise its launches
         const int guess = (s->has_secondary && n_px >= (1u << 19)) ? 1 : 0;
         const bool three = forced_lpp(s) < 0 && mixed_candidate(s, n_px);
         if (s->frames < 4) {
             which = (s->frames & 1) ? 1 - guess : guess;  // two frames each: the first one is cold
+            measuring = true;
         } else if (three && s->frames < 6) {
             which = 2;
+            measuring = true;
         } else {
             which = (s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
             if (three && s->best_ms[2] >= 0.0f && s->best_ms[2] < s->best_ms[which]) which = 2;
@@ -517,14 +678,19 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     }
     int lpp = forced_lpp(s);
     if (lpp < 0) lpp = which == 2 ? 0 : 1;
-    const int slot = which == 2 ? 2 : 0;  // where a megakernel frame's time is recorded
+    F.best_slot = which == 2 ? 2 : 0;  // where a megakernel frame's time is recorded
     s->frames++;
     if (which == 1) {
         rtc_stats local{};
-        int rc = render_wavefront(s, P, stream, &local);
+        int rc = render_wavefront(s, P, stream, &local);  // synchronous: its queue counters decide about a redo
         if (rc != RTC_ERR_CAPACITY + 1000) {
             if (rc == RTC_OK && (s->best_ms[1] < 0.0f || local.kernel_ms < s->best_ms[1])) s->best_ms[1] = local.kernel_ms;
-            if (stats) *stats = local;
+            CUDA_TRY(cudaEventRecord(s->rev2[slot], stream));
+            F.stats = local;
+            F.state = 2;
+            F.rc = rc;
+            s->seq_next++;
+            *slot_out = slot;
             return rc;
         }
         s->best_ms[1] = 1e30f;  // queue overflow: this scene stays with the megakernel; redo the frame below
@@ -539,9 +705,11 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         const char* e = std::getenv("RTC_LPT");
         return e ? std::atoi(e) : 1;
     }();
-    const bool lpt = lpt_env == 2 || (lpt_env == 1 && !spread_rows);
+    const bool lpt = lpt_env == 2 || (lpt_env == 1 && !tg.spread_rows);
+    F.lpt = lpt;
     if (lpt) {
         if (s->tile_cap < n_tiles) {
+            CUDA_TRY(cudaStreamSynchronize(stream));  // frames of the old size may still read the arrays
             if (s->d_tile_cost) cudaFree(s->d_tile_cost);
             if (s->d_tile_order) cudaFree(s->d_tile_order);
             s->d_tile_cost = s->d_tile_order = nullptr;
@@ -558,60 +726,152 @@ static int render_common(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         P.heavy_tiles = s->d_tile_cost + n_tiles + 4 * ((n_tiles + 1023) / 1024);
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
-    CUDA_TRY(cudaEventRecord(s->ev0, stream));
+    CUDA_TRY(cudaEventRecord(s->rev0[slot], stream));
     // The mixed kernel needs the order of a previous frame.  Without one (first frame of a size; canvases in mapped host
     // memory, which keep the strided order) the candidate is two lanes per pixel everywhere: measured on the 1/8 partition
     // of dragons.json 1080p without an order, 0.49 -> 0.39 ms.
     if (lpp == 0 && !P.tile_order) lpp = 2;
+    F.lpp = lpp;
     P.n_items *= (unsigned long long)(lpp ? lpp : 1);
     CUDA_TRY((cudaError_t)launch_mega(s, P, lpp, stream));
-    CUDA_TRY(cudaEventRecord(s->ev1, stream));
-    unsigned long long c[8];
-    CUDA_TRY(cudaMemcpyAsync(c, s->d_counters, sizeof c, cudaMemcpyDeviceToHost, stream));
-    CUDA_TRY(cudaStreamSynchronize(stream));
-    float ms = 0;
-    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    if (lpt) {  // the next frame's order; runs behind this call, ahead of the next frame on the same stream
+    if (lpt) {  // the next frame's order, made from this frame's costs right behind the kernel, on the same stream
         CUDA_TRY((cudaError_t)launch_tile_order(s->d_tile_cost, s->d_counters + 6, s->d_tile_cost + n_tiles, s->d_tile_order,
                                                 (unsigned)n_tiles, stream));
         s->order_tiles = n_tiles;
     }
-#ifdef RTC_TRIP_PROBE
-    std::fprintf(stderr, "trip probe: max trip %.1f us, trips %llu, > 50 us: %llu, > 20 us: %llu (kernel %.3f ms)\n", c[6] / 1965.0,
-                 c[7] & 0xffffffffull, (c[7] >> 32) & 0xffffull, c[7] >> 48, ms);
-#endif
-    if (stats) {
-        stats->primary_rays = c[1];
-        stats->shadow_rays = c[2];
-        stats->secondary_rays = c[3];
-        stats->pixels = P.rows * cam->hsize;
-        stats->kernel_ms = ms;
-        stats->launches = lpt ? 3 : 1;  // render_kernel (+ the two kernels of tile_order.cu)
-        stats->kernel = lpp != 1 ? 2u : 0u;
-        stats->shadow_rays_culled = c[5];
-    }
-    if (s->best_ms[slot] < 0.0f || ms < s->best_ms[slot]) s->best_ms[slot] = ms;
-    if (c[4]) {
-        char buf[224];
-        std::snprintf(buf, sizeof buf,
-                      "render: per-ray capacity exceeded (bits %llu: 1=texture lookup out of range, 2=pattern stack, "
-                      "4=CSG list, 8=BVH stack, 32=pixel sum out of the accumulator's range)",
-                      c[4]);
-        return fail(RTC_ERR_CAPACITY, buf);
-    }
+    CUDA_TRY(cudaEventRecord(s->rev1[slot], stream));
+    CUDA_TRY(cudaMemcpyAsync(s->h_counters + 8 * slot, s->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaEventRecord(s->rev2[slot], stream));
+    F.state = 1;
+    s->seq_next++;
+    *slot_out = slot;
+    if (wait || measuring) return resolve_frame(s, slot);
     return RTC_OK;
+}
+
+// Hands out the statistics of the OLDEST frame not handed out yet and frees its slot.
+static int pop_frame(rtc_scene* s, rtc_stats* stats) {
+    if (s->seq_pop == s->seq_next) return fail(RTC_ERR_INVALID, "no frame in flight");
+    const int slot = (int)(s->seq_pop % rtc_scene::kRing);
+    int rc = resolve_frame(s, slot);
+    if (stats) *stats = s->ring[slot].stats;
+    s->ring[slot].state = 0;
+    s->seq_pop++;
+    return rc;
+}
+
+static void add_stats(rtc_stats* sum, const rtc_stats& a) {
+    sum->primary_rays += a.primary_rays;
+    sum->shadow_rays += a.shadow_rays;
+    sum->secondary_rays += a.secondary_rays;
+    sum->pixels += a.pixels;
+    sum->shadow_rays_culled += a.shadow_rays_culled;
+    sum->launches += a.launches;
+    sum->kernel_ms = std::fmax(sum->kernel_ms, a.kernel_ms);  // the devices work side by side
+    sum->kernel = a.kernel > sum->kernel ? a.kernel : sum->kernel;
+}
+
+// One frame, all devices of the scene.  A scene on one device: `part` as given.  A replicated scene (rtc_set_devices)
+// rendering a WHOLE frame: device k of n takes the interleaved 8-row tiles k, k + n, ... and stores them at their frame
+// positions into the same target (device 0's memory through peer access, or mapped host memory each over its own PCIe
+// link); the caller's stream continues when all of them are through.
+static int render_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, Target tg,
+                        cudaStream_t stream, bool wait, rtc_stats* stats) {
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    if (!s) return fail(RTC_ERR_INVALID, "render: NULL scene");
+    const bool whole = !part || part->n_parts <= 1;
+    if (s->replicas.empty() || !whole) {
+        int slot = -1;
+        int rc = enqueue_frame(s, cam, max_depth, part, tg, stream, wait, &slot);
+        if (!wait || slot < 0) return rc;
+        while (s->seq_next - s->seq_pop > 1) pop_frame(s, nullptr);  // frames put on the stream earlier and never fetched
+        const int rp = pop_frame(s, stats);
+        return rc ? rc : rp;
+    }
+    const unsigned n = 1u + (unsigned)s->replicas.size();
+    tg.full_frame = true;
+    CUDA_TRY(cudaSetDevice(s->device));
+    // the replicas start when the caller's stream has reached this point (its earlier work may still read the target)
+    CUDA_TRY(cudaEventRecord(s->ev0, stream));
+    int rc = RTC_OK;
+    std::vector<int> slots(n, -1);
+    for (unsigned k = 0; k < n && rc == RTC_OK; k++) {
+        rtc_scene* r = k == 0 ? s : s->replicas[k - 1];
+        rtc_partition p = {8u, k, n};
+        cudaStream_t st = k == 0 ? stream : r->own_stream;
+        if (k > 0) {
+            CUDA_TRY(cudaSetDevice(r->device));
+            CUDA_TRY(cudaStreamWaitEvent(st, s->ev0, 0));
+        }
+        rc = enqueue_frame(r, cam, max_depth, &p, tg, st, false, &slots[k]);
+    }
+    CUDA_TRY(cudaSetDevice(s->device));
+    for (unsigned k = 1; k < n; k++) {
+        rtc_scene* r = s->replicas[k - 1];
+        if (slots[k] >= 0 && r->ring[slots[k]].state != 0) CUDA_TRY(cudaStreamWaitEvent(stream, r->rev2[slots[k]], 0));
+    }
+    if (!wait) return rc;
+    for (unsigned k = 0; k < n; k++) {
+        rtc_scene* r = k == 0 ? s : s->replicas[k - 1];
+        if (slots[k] < 0) continue;
+        while (r->seq_next - r->seq_pop > 1) pop_frame(r, nullptr);
+        rtc_stats one{};
+        int rk = pop_frame(r, &one);
+        if (rk && !rc) rc = rk;
+        if (stats) add_stats(stats, one);
+    }
+    CUDA_TRY(cudaSetDevice(s->device));
+    return rc;
 }
 
 int rtc_render_device(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_rgb,
                       void* stream, rtc_stats* stats) {
     if (!d_rgb) return fail(RTC_ERR_INVALID, "rtc_render_device: d_rgb is NULL");
-    return render_common(s, cam, max_depth, part, d_rgb, nullptr, (cudaStream_t)stream, stats);
+    Target tg;
+    tg.rgb = d_rgb;
+    return render_frame(s, cam, max_depth, part, tg, (cudaStream_t)stream, true, stats);
 }
 
 int rtc_render_device_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                             double* d_frame, void* stream, rtc_stats* stats) {
     if (!d_frame) return fail(RTC_ERR_INVALID, "rtc_render_device_frame: d_frame is NULL");
-    return render_common(s, cam, max_depth, part, d_frame, nullptr, (cudaStream_t)stream, stats, true);
+    Target tg;
+    tg.rgb = d_frame;
+    tg.full_frame = true;
+    return render_frame(s, cam, max_depth, part, tg, (cudaStream_t)stream, true, stats);
+}
+
+int rtc_render_device_async(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* d_frame,
+                            void* stream) {
+    if (!d_frame) return fail(RTC_ERR_INVALID, "rtc_render_device_async: d_frame is NULL");
+    Target tg;
+    tg.rgb = d_frame;
+    tg.full_frame = true;
+    return render_frame(s, cam, max_depth, part, tg, (cudaStream_t)stream, false, nullptr);
+}
+
+int rtc_stats_fetch(rtc_scene* s, rtc_stats* stats_out, uint32_t max_frames, uint32_t* n_out) {
+    if (n_out) *n_out = 0;
+    if (!s) return fail(RTC_ERR_INVALID, "rtc_stats_fetch: NULL scene");
+    int rc = RTC_OK;
+    uint32_t n = 0;
+    while (s->seq_pop != s->seq_next && (n < max_frames || !stats_out)) {
+        rtc_stats sum{};
+        int rk = pop_frame(s, &sum);
+        if (rk && !rc) rc = rk;
+        for (rtc_scene* r : s->replicas) {  // a replicated frame has one entry per device
+            if (r->seq_pop == r->seq_next) continue;
+            rtc_stats one{};
+            rk = pop_frame(r, &one);
+            if (rk && !rc) rc = rk;
+            add_stats(&sum, one);
+        }
+        if (stats_out) stats_out[n] = sum;
+        n++;
+    }
+    if (n_out) *n_out = n;
+    cudaSetDevice(s->device);
+    return rc;
 }
 
 static int ensure_frame(rtc_scene* s, size_t bytes) {
@@ -624,20 +884,27 @@ static int ensure_frame(rtc_scene* s, size_t bytes) {
     return RTC_OK;
 }
 
-// copies the packed partition rows into their places in the caller's full frame
+// Copies the packed partition rows into their places in the caller's full frame: the tiles of a partition are
+// tile_rows rows each, n_parts tiles apart -- one strided 2-D copy for all full tiles, one more for a ragged last tile.
 static int scatter_rows(const rtc_camera* cam, const rtc_partition* part, const void* d_src, void* h_dst, size_t px_bytes) {
-    size_t row_bytes = (size_t)cam->hsize * px_bytes;
+    const size_t row_bytes = (size_t)cam->hsize * px_bytes;
     if (!part || part->n_parts <= 1) {
         CUDA_TRY(cudaMemcpy(h_dst, d_src, row_bytes * cam->vsize, cudaMemcpyDeviceToHost));
         return RTC_OK;
     }
-    uint64_t tr = part->tile_rows, n_tiles = (cam->vsize + tr - 1) / tr, packed = 0;
-    for (uint64_t t = part->part; t < n_tiles; t += part->n_parts) {
-        uint64_t y0 = t * tr, y1 = y0 + tr < cam->vsize ? y0 + tr : cam->vsize;
-        CUDA_TRY(cudaMemcpy((char*)h_dst + y0 * row_bytes, (const char*)d_src + packed * row_bytes, (y1 - y0) * row_bytes,
-                            cudaMemcpyDeviceToHost));
-        packed += y1 - y0;
-    }
+    const uint64_t tr = part->tile_rows, n_tiles = (cam->vsize + tr - 1) / tr;
+    if (part->part >= n_tiles) return RTC_OK;
+    const uint64_t mine = (n_tiles - part->part + part->n_parts - 1) / part->n_parts;  // tiles of this partition
+    const uint64_t last = part->part + (mine - 1) * part->n_parts;                       // index of its last tile
+    const bool ragged = (last + 1) * tr > cam->vsize;
+    const uint64_t full = ragged ? mine - 1 : mine;
+    const size_t tile_bytes = (size_t)tr * row_bytes;
+    if (full)
+        CUDA_TRY(cudaMemcpy2D((char*)h_dst + (size_t)part->part * tile_bytes, (size_t)part->n_parts * tile_bytes, d_src, tile_bytes,
+                              tile_bytes, full, cudaMemcpyDeviceToHost));
+    if (ragged)
+        CUDA_TRY(cudaMemcpy((char*)h_dst + (size_t)last * tile_bytes, (const char*)d_src + (size_t)full * tile_bytes,
+                            (size_t)(cam->vsize - last * tr) * row_bytes, cudaMemcpyDeviceToHost));
     return RTC_OK;
 }
 
@@ -655,7 +922,7 @@ void rtc_host_free(void* p) {
 }
 
 // The device-side address of a pinned + mapped host buffer, or NULL for pageable memory.
-static double* mapped_device_pointer(const void* host) {
+static void* mapped_device_pointer(const void* host) {
     static const bool off = [] {
         const char* e = std::getenv("RTC_NO_ZEROCOPY");
         return e && e[0] == '1';
@@ -667,7 +934,7 @@ static double* mapped_device_pointer(const void* host) {
         return nullptr;
     }
     if (at.type != cudaMemoryTypeHost || !at.devicePointer) return nullptr;
-    return static_cast<double*>(at.devicePointer);
+    return at.devicePointer;
 }
 
 int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, double* rgb_out,
@@ -676,12 +943,20 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
     CUDA_TRY(cudaSetDevice(s->device));
     // Canvas in pinned memory (rtc_host_alloc): the kernel stores every finished pixel straight into it
     // across PCIe, overlapped with the rendering of the others -- no staging frame, no copy afterwards.
-    if (double* mapped = mapped_device_pointer(rgb_out))
-        return render_common(s, cam, max_depth, part, mapped, nullptr, 0, stats, true, true);
+    if (void* mapped = mapped_device_pointer(rgb_out)) {
+        Target tg;
+        tg.rgb = static_cast<double*>(mapped);
+        tg.full_frame = tg.spread_rows = true;
+        return render_frame(s, cam, max_depth, part, tg, 0, true, stats);
+    }
+    const bool whole = !part || part->n_parts <= 1;
     uint64_t rows = rtc_partition_rows(cam->vsize, part);
     int rc = ensure_frame(s, (size_t)rows * cam->hsize * 3 * sizeof(double) + 16);
     if (rc) return rc;
-    rc = render_common(s, cam, max_depth, part, s->d_frame, nullptr, 0, stats);
+    Target tg;
+    tg.rgb = s->d_frame;
+    tg.full_frame = whole;
+    rc = render_frame(s, cam, max_depth, part, tg, 0, true, stats);
     if (rc) return rc;
     return scatter_rows(cam, part, s->d_frame, rgb_out, 3 * sizeof(double));
 }
@@ -690,10 +965,22 @@ int rtc_render_rgba8(rtc_scene* s, const rtc_camera* cam, int max_depth, const r
                      rtc_stats* stats) {
     if (!s || !cam || !rgba_out) return fail(RTC_ERR_INVALID, "rtc_render_rgba8: NULL argument");
     CUDA_TRY(cudaSetDevice(s->device));
+    // as rtc_render: a pinned + mapped buffer (rtc_host_alloc; the lib.zig twin's pixel buffer is one) is written by
+    // the kernel itself, 4 bytes per pixel over PCIe while the frame renders
+    if (void* mapped = mapped_device_pointer(rgba_out)) {
+        Target tg;
+        tg.rgba = static_cast<unsigned char*>(mapped);
+        tg.full_frame = tg.spread_rows = true;
+        return render_frame(s, cam, max_depth, part, tg, 0, true, stats);
+    }
+    const bool whole = !part || part->n_parts <= 1;
     uint64_t rows = rtc_partition_rows(cam->vsize, part);
     int rc = ensure_frame(s, (size_t)rows * cam->hsize * 4 + 16);
     if (rc) return rc;
-    rc = render_common(s, cam, max_depth, part, nullptr, (unsigned char*)s->d_frame, 0, stats);
+    Target tg;
+    tg.rgba = reinterpret_cast<unsigned char*>(s->d_frame);
+    tg.full_frame = whole;
+    rc = render_frame(s, cam, max_depth, part, tg, 0, true, stats);
     if (rc) return rc;
     return scatter_rows(cam, part, s->d_frame, rgba_out, 4);
 }

@@ -337,3 +337,128 @@ def test_baseline_config_full_size(pkg, oracle, name, w, h):
     assert np.array_equal(rgba[..., :3], oracle.quantise(canvas.pixels)) and (rgba[..., 3] == 255).all()
     info.world.close()
     ref.close()
+
+
+def test_async_frames_and_stats_fetch(pkg):
+    """rtc_render_device_async only puts frames on the stream; rtc_stats_fetch hands out their statistics in order.
+    Same frame, same counts as the synchronous call; frames of one scene put on DIFFERENT streams stay ordered
+    (the tile-order kernels of frame k must not overlap the memsets of frame k + 1)."""
+    import torch
+    s = scenes.shipped_scene("teapot")
+    text, assets, (w, h) = (s[0], s[1], (400, 240)) if s else (scenes.SMOKE_SCENE, "", (160, 96))
+    info = pkg.parse_scene(text, assets, w, h)
+    cam, wld = info.camera, info.world
+    ref = torch.empty((h, w, 3), dtype=torch.float64, device="cuda")
+    for _ in range(7):  # past the library's first-frames measurement
+        want = cam.render_device_frame(wld, ref.data_ptr())
+    frames = [torch.full((h, w, 3), float("nan"), dtype=torch.float64, device="cuda") for _ in range(6)]
+    side = torch.cuda.Stream()
+    for i, f in enumerate(frames):
+        stream = side.cuda_stream if i % 2 else torch.cuda.current_stream().cuda_stream
+        cam.render_device_async(wld, f.data_ptr(), stream=stream)
+    stats = wld.fetch_stats()
+    torch.cuda.synchronize()
+    assert len(stats) == len(frames)
+    for f, st in zip(frames, stats):
+        assert torch.equal(f, ref)
+        assert (st.primary_rays, st.shadow_rays, st.secondary_rays) == (want.primary_rays, want.shadow_rays, want.secondary_rays)
+        assert st.kernel_ms > 0
+    assert wld.fetch_stats() == []
+    # a synchronous call after un-fetched asynchronous ones returns ITS OWN statistics
+    cam.render_device_async(wld, frames[0].data_ptr())
+    cam.look_at((0, 3, -8), (0, 1, 0), (0, 1, 0))
+    moved = cam.render_device_frame(wld, frames[1].data_ptr())
+    assert moved.primary_rays == w * h and not torch.equal(frames[1], ref)
+    wld.close()
+
+
+@pytest.mark.parametrize("name", ["dragons", "teapot", "cover", "mesh"])
+def test_lean_and_general_kernels_are_bit_identical(pkg, tmp_path, name):
+    """render_kernel<MESH, LPP, LEAN>: scenes without CSG, guard boxes and non-solid patterns run an instantiation that
+    carries none of that code; RTC_LEAN=0 keeps the general one.  Same frame, same ray counts, bit for bit."""
+    if name == "mesh":
+        scenes.write_mesh_obj(str(tmp_path / "torus.obj"), smooth=True, groups=False)
+        text, assets, (w, h) = scenes.mesh_scene("torus.obj"), str(tmp_path), (200, 120)
+    else:
+        s = scenes.shipped_scene(name)
+        if s is None:
+            pytest.skip("reference assets not staged")
+        text, assets, (w, h) = s[0], s[1], (320, 180)
+    out = {}
+    try:
+        for key, lean in (("lean", "1"), ("general", "0")):
+            os.environ["RTC_LEAN"] = lean  # read when the scene is created
+            info = pkg.parse_scene(text, assets, w, h)
+            c = info.camera.render(info.world)
+            out[key] = (c.pixels.copy(), (c.stats.primary_rays, c.stats.shadow_rays, c.stats.secondary_rays))
+            info.world.close()
+    finally:
+        os.environ.pop("RTC_LEAN", None)
+    assert out["lean"][0].any()
+    assert np.array_equal(out["lean"][0], out["general"][0]) and out["lean"][1] == out["general"][1]
+
+
+def test_two_scenes_keep_their_shared_memory(pkg, tmp_path):
+    """the dynamic shared memory limit belongs to the kernel, not to a scene -- a deep scene created first,
+    a shallow one second, then the deep one rendered again."""
+    scenes.write_mesh_obj(str(tmp_path / "torus.obj"), smooth=True, groups=False)
+    deep = pkg.parse_scene(scenes.mesh_scene("torus.obj"), str(tmp_path), 96, 64)
+    a = deep.camera.render(deep.world).pixels.copy()
+    shallow = pkg.parse_scene(scenes.default_world(), "")
+    shallow.camera.render(shallow.world)
+    b = deep.camera.render(deep.world).pixels
+    assert np.array_equal(a, b)
+
+
+def test_rgba8_into_pinned_memory_is_zero_copy_and_equal(pkg):
+    """rtc_render_rgba8 into rtc_host_alloc memory (what the lib.zig twin's pixel buffer is): the kernel writes it
+    directly; same bytes as the staged path, whole frame and partitions."""
+    info = pkg.parse_scene(scenes.SMOKE_SCENE, "", 163, 97)
+    staged, _ = info.camera.render_rgba8(info.world)
+    pinned = pkg.pinned_empty((97, 163, 4), dtype=np.uint8)
+    pinned[:] = 0
+    st = pkg.rtc_stats()
+    import ctypes
+    for part in (None, (8, 0, 2), (8, 1, 2)):
+        keep, pref = info.camera._part(part)
+        if part == (8, 0, 2):
+            pinned[:] = 0
+        pkg._check(pkg.lib().rtc_render_rgba8(info.world._h, ctypes.byref(info.camera.c), 5, pref, pinned.ctypes.data, ctypes.byref(st)))
+        if part is None or part == (8, 1, 2):
+            assert np.array_equal(pinned, staged)
+    part_only, _ = info.camera.render_rgba8(info.world, partition=(8, 1, 3))  # staged + strided 2-D copy
+    rows = [y for y in range(97) if (y // 8) % 3 == 1]
+    assert np.array_equal(part_only[rows], staged[rows])
+    other = [y for y in range(97) if (y // 8) % 3 != 1]
+    assert not part_only[other].any()
+    pkg.free_pinned(pinned)
+
+
+def test_replicated_scene_uses_all_devices(pkg):
+    """rtc_set_devices(n): ONE process, the scene built once and replicated, a whole-frame call split over the devices
+    (interleaved 8-row tiles, peer stores into device 0's frame / into the caller's pinned canvas): bit-identical."""
+    import torch
+    if pkg.device_count() < 2:
+        pytest.skip("one GPU visible")
+    n = min(pkg.device_count(), 4)
+    s = scenes.shipped_scene("dragons")
+    text, assets, (w, h) = (s[0], s[1], (480, 270)) if s else (scenes.SMOKE_SCENE, "", (160, 96))
+    blob, cam = pkg.load_blob(text, assets, w, h)
+    one = pkg.World(blob, 0)
+    camera = pkg.Camera(cam)
+    want = camera.render(one)
+    many = pkg.World(blob, 0, devices=n)
+    got = camera.render(many)                              # pageable canvas: assembled on device 0, one copy
+    assert np.array_equal(got.pixels, want.pixels) and got.stats.rays == want.stats.rays
+    pinned = pkg.pinned_empty((h, w, 3))
+    got2 = camera.render(many, out=pinned)                  # pinned canvas: every device stores its rows itself
+    assert np.array_equal(got2.pixels, want.pixels)
+    frame = torch.zeros((h, w, 3), dtype=torch.float64, device="cuda:0")
+    st = camera.render_device_frame(many, frame.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(frame.cpu().numpy(), want.pixels) and st.rays == want.stats.rays
+    rgba, _ = camera.render_rgba8(many)
+    assert np.array_equal(rgba[..., :3], want.to_image())
+    pkg.free_pinned(pinned)
+    many.close()
+    one.close()
