@@ -5,16 +5,19 @@ Workload (config.workload): scenes/dragons.json rendered at 1920x1080, recursion
 the configuration BASELINE.json quotes its target on.  One "step" = one frame.
 
   value   Mrays/s (primary + shadow + secondary rays, counted on the device) with the scene resident
-          in HBM and the frame left in HBM (rtc_render_device), CUDA-event timed, L2 flushed between
-          steps (the scene, ~30 MB, would otherwise sit in the 126 MB L2).
+          in HBM and the frame left in HBM: frames are put on the stream back to back
+          (rtc_render_device_async, no host round trip per frame), every step bracketed by CUDA events
+          on that stream, the L2 flushed between steps (the scene would otherwise sit in the 126 MB L2).
   e2e     the same metric through the reference-facing call Camera.render(world) -> host Canvas
-          (rtc_render): camera in, kernel, device->host copy of the f64 frame, all inside the timed
-          region.  The world stays uploaded between frames, the reference's own "preheated"
-          convention (README.md:122-125, lib.zig:166-190).
-  N > 1   one process per GPU (torchrun); rank r renders the interleaved 8-row tiles r, r+N, ... and
-          the packed rows are gathered to rank 0 over NCCL.  Strong scaling (same frame).
-  --impl reference   the CPU restatement of the reference algorithm (oracle/, all host threads) on a
-          bounded sample of the same frame (the reference itself is Zig: unavailable on this box).
+          (rtc_render): camera in, kernel, f64 frame in host memory, all inside the timed region.
+          The world stays uploaded between frames, the reference's own "preheated" convention
+          (README.md:122-125, lib.zig:166-190).  e2e_rgba8: the lib.zig twin (rtc_render_rgba8).
+  N > 1   one process per GPU (torchrun).  Rank 0 parses the scene and broadcasts the blob (NCCL); the tiles of
+          the frame are dealt to the ranks by their cost in the frame before (rtc_scene_share_tiles), every
+          rank's kernel stores its pixels straight into rank 0's frame over NVLink, one device barrier per frame.
+          Strong scaling (same frame).
+  --impl reference   the CPU restatement of the reference algorithm (oracle/, all host threads) on the
+          SAME full frame, one frame per step (the reference itself is Zig: unavailable on this box).
 """
 import argparse
 import importlib
@@ -28,47 +31,42 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 SCENE, WIDTH, HEIGHT, DEPTH, TILE_ROWS = "dragons", 1920, 1080, 5, 8
-# algorithmic bytes per ray for dragons.json = 13 two-child f32 nodes x 64 B +
-# 4 triangles x 72 B + 6 instance root tests x 64 B
+# SURVEY.md §8(d), fixed there so that builder and judge use the same numbers.  dragons.json: bytes/ray = 13
+# two-child f32 nodes x 64 B + 4 triangles x 72 B + 6 instance root tests x 64 B; flops/ray = 19 node tests x 24 +
+# 4 triangle tests x 45 + 56 (ray transform).
 BYTES_PER_RAY = 1504
+FLOPS_PER_RAY = 19 * 24 + 4 * 45 + 56
+# the other BASELINE.json configs (reported in `configs`; the headline stays dragons)
+CONFIGS = [("fresnel_600", "fresnel", 600, 600), ("cover_1080", "cover", 1920, 1080), ("teapot_1080", "teapot", 1920, 1080),
+           ("csg_2160", "csg", 3840, 2160), ("skybox_2160", "skybox", 3840, 2160)]
+CFG_FLOPS = {"fresnel": 225.0, "cover": 1604.0}   # SURVEY.md §8(d) analytic scenes: f64 flops per ray
+CFG_BYTES = {"teapot": 992.0}                      # mesh scenes: node + triangle bytes per ray
 
 
-def scene_source():
+def scene_source(name=SCENE):
     from tests import scenes
-    s = scenes.shipped_scene(SCENE)
+    s = scenes.shipped_scene(name)
     if s is None:
         raise SystemExit("bench: assets/_ref/scenes/%s.json is not staged; run __graft_entry__.build() where "
-                         "/root/reference is mounted" % SCENE)
+                         "/root/reference is mounted" % name)
     return s
 
 
-def ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum of one render_kernel launch of THIS workload, from the
-    committed `ncu --set full` capture (profiles/traffic.json, written by profiles/summarize_ncu.py)."""
+def load_json(*path):
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            t = json.load(f)
-        return float(t["dram_bytes_per_launch"]), t.get("source", "")
-    except Exception:
-        return None, ""
-
-
-def peaks():
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
-    except Exception:
-        return 6650.0, "fallback"
-
-
-def l2_fraction(achieved_gbs):
-    """The same figure against the L2-resident copy bandwidth measured on a B200 by tools/peaks (committed)."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r1_alu_l2_peaks.json")) as f:
-            l2 = float(json.load(f)["l2_copy_gbs"])
-        return {"l2_copy_peak": l2, "frac_of_l2_copy": achieved_gbs / l2}
-    except Exception:
+        with open(os.path.join(ROOT, *path)) as f:
+            return json.load(f)
+    except Exception:  # noqa: BLE001
         return {}
+
+
+def measured_peaks():
+    """Denominators: MEASURED_PEAKS.json (driver-written HBM copy GB/s) and tools/peaks on a B200 (committed):
+    FP64 FMA TFLOP/s, L2-resident copy GB/s.  The issue-rate peak is arithmetic: SMs x 4 schedulers x SM clock."""
+    drv, alu = load_json("MEASURED_PEAKS.json"), load_json("profiles", "r1_alu_l2_peaks.json")
+    return {"hbm_gbs": float(drv.get("hbm_gbs", 6650.0)), "hbm_source": "measured (MEASURED_PEAKS.json)" if drv else "fallback",
+            "fp64_tflops": float(alu.get("fp64_fma_tflops", 33.86)), "l2_gbs": float(alu.get("l2_copy_gbs", 6973.0)),
+            "sms": int(alu.get("sms", 148))}
 
 
 class ClockSampler(threading.Thread):
@@ -87,7 +85,7 @@ class ClockSampler(threading.Thread):
             self.nv = pynvml
             self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
-        except Exception:
+        except Exception:  # noqa: BLE001
             self.h = None
 
     def sample_nvml(self):
@@ -118,7 +116,7 @@ class ClockSampler(threading.Thread):
                     self.sample_nvml()
                 else:
                     self.sample_smi()
-            except Exception:
+            except Exception:  # noqa: BLE001
                 pass
             time.sleep(0.001 if self.h is not None else 0.05)
 
@@ -128,23 +126,18 @@ class ClockSampler(threading.Thread):
                 "samples": len(s), "source": "nvml" if self.h is not None else "nvidia-smi"}
 
 
-def cpu_sample(threads, bands=8, frac=0.125):
-    """Oracle on `bands` evenly spaced row bands covering `frac` of the frame -> (rays, seconds, desc)."""
+def cpu_frame(name, width, height, threads, scene=None):
+    """The oracle on the WHOLE frame, one task per row on `threads` host threads (camera.zig:88-97)
+    -> (rays, seconds, description, scene handle for re-use)."""
     from oracle import oracle_py
-    text, assets = scene_source()
-    sc = oracle_py.OracleScene(json_text=text, asset_dir=assets, width=WIDTH, height=HEIGHT)
-    rows = max(1, int(HEIGHT * frac / bands))
-    rays, secs = 0, 0.0
-    import numpy as np
-    out = np.zeros((HEIGHT, WIDTH, 3))
-    for b in range(bands):
-        y0 = int((b + 0.5) * HEIGHT / bands) - rows // 2
-        t = time.perf_counter()
-        _, c = sc.render(threads=threads, y0=y0, y1=y0 + rows)
-        secs += time.perf_counter() - t
-        rays += c["primary"] + c["shadow"] + c["secondary"]
-    return rays, secs, "%d bands x %d rows of the %dx%d frame (%.1f%% of the pixels)" % (
-        bands, rows, WIDTH, HEIGHT, 100.0 * bands * rows / HEIGHT)
+    if scene is None:
+        text, assets = scene_source(name)
+        scene = oracle_py.OracleScene(json_text=text, asset_dir=assets, width=width, height=height)
+    t = time.perf_counter()
+    _, c = scene.render(threads=threads)
+    secs = time.perf_counter() - t
+    rays = c["primary"] + c["shadow"] + c["secondary"]
+    return rays, secs, "the whole %dx%d frame, %d rows as %d tasks on %d threads" % (width, height, height, height, threads), scene
 
 
 def base_line(args, n):
@@ -152,30 +145,33 @@ def base_line(args, n):
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "scenes/dragons.json 1920x1080 depth 5 (6 x dragon.obj, 140,940 smooth triangles, "
                                    "4 lights); the scene file IS the input, there is no random data",
-                       "l2": "flushed between steps (256 MiB memset)", "partition": "interleaved %d-row tiles" % TILE_ROWS,
-                       "tile_order": "device-resident frames: tiles handed out in the order of their cost in the previous frame "
-                                     "(scheduling only: every ray of every pixel is traced in every step, frames bit-identical; "
-                                     "RTC_LPT=0 for the plain order); host canvases: strided row order"}}
+                       "l2": "flushed between steps (256 MiB memset)",
+                       "partition": "N > 1: the frame's 8x4-pixel tiles dealt to the ranks by their cost in the frame before "
+                                    "(fallback without symmetric memory: interleaved %d-row tiles + NCCL gather)" % TILE_ROWS,
+                       "tile_order": "device-resident frames: tiles handed out in the order of their cost in an earlier frame of the "
+                                     "same view (scheduling only: every ray of every pixel is traced in every step, frames "
+                                     "bit-identical; first_frame_ms is the frame without any order); host canvases: strided row order"}}
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    for _ in range(args.warmup):
-        cpu_sample(threads, bands=2, frac=0.004)
+    scene = None
+    for _ in range(min(args.warmup, 1)):  # a frame is seconds of CPU work: one warm-up frame pages everything in
+        _, _, _, scene = cpu_frame(SCENE, WIDTH, HEIGHT, threads, scene)
     rays = secs = 0
     desc = ""
     for _ in range(args.steps):
-        r, s, desc = cpu_sample(threads)
+        r, s, desc, scene = cpu_frame(SCENE, WIDTH, HEIGHT, threads, scene)
         rays, secs = rays + r, secs + s
     v = rays / secs / 1e6
     line = base_line(args, args.gpus)
     line.update({"impl": "reference", "value": v, "ms_per_step": 1e3 * secs / args.steps,
                  "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": desc},
                  "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                 "note": "C++ restatement of the reference CPU algorithm (oracle/); the Zig reference cannot be built "
-                         "on this box; ms_per_step is the time of the SAMPLE, not of a full frame"})
+                 "note": "C++ restatement of the reference CPU algorithm (oracle/: all-hit lists, per-leaf transforms, the "
+                         "reference's divide(8) group tree), one step = the whole frame; the Zig reference cannot be built on this box"})
     emit(line)
 
 
@@ -195,6 +191,96 @@ def quiet_stdout():
     os.dup2(2, 1)
 
 
+def roofline_block(rays_per_launch, k_ms, pk):
+    """The dominant kernel against the roofs it could hit.  ncu (profiles/r2_*_render_kernel.txt) says which binds:
+    instruction issue at the occupancy 128 registers allow -- neither the FP64 pipe nor any memory level is near
+    its peak.  achieved (issue) = warp instructions of one launch (from the committed ncu capture of this workload)
+    / the CUDA-event launch time measured here."""
+    prof = load_json("profiles", "r2_roofline_inputs.json")
+    sec = k_ms * 1e-3
+    issue_peak = pk["sms"] * 4 * 1.965e9 / 1e9  # G warp-instructions / s
+    inst = prof.get("warp_instructions_per_launch")
+    out = {"bound": "issue", "unit": "Ginst/s", "peak": issue_peak,
+           "peak_source": "%d SMs x 4 warp schedulers x 1 instruction / cycle x 1.965 GHz" % pk["sms"],
+           "achieved": (inst / sec / 1e9) if inst else None}
+    out["frac"] = out["achieved"] / issue_peak if inst else None
+    out["model"] = ("warp instructions per launch (%s) / launch time; ncu of the same launch: issue slots %s %% busy, FP64 pipe %s %%, "
+                    "%s of 32 threads active per instruction, DRAM %s %% of peak" % (
+                        prof.get("source", "no capture committed"), prof.get("issue_active_pct"), prof.get("fp64_pipe_pct"),
+                        prof.get("threads_per_inst"), prof.get("dram_pct")))
+    out["issue_active_pct"] = prof.get("issue_active_pct")
+    out["fp64_pipe_pct"] = prof.get("fp64_pipe_pct")
+    out["traffic"] = prof.get("dram_bytes_per_launch")
+    out["traffic_source"] = prof.get("source")
+    # SURVEY.md §8(d) figures, each against its own MEASURED roof
+    flops = FLOPS_PER_RAY * rays_per_launch / sec / 1e12
+    gbs = BYTES_PER_RAY * rays_per_launch / sec / 1e9
+    out["alu"] = {"flops_per_ray": FLOPS_PER_RAY, "achieved": flops, "peak": pk["fp64_tflops"], "unit": "TFLOP/s (f64)",
+                  "frac": flops / pk["fp64_tflops"]}
+    out["model_bytes"] = {"bytes_per_ray": BYTES_PER_RAY, "achieved": gbs, "unit": "GB/s", "peak_l2": pk["l2_gbs"],
+                          "frac_of_l2": gbs / pk["l2_gbs"], "peak_hbm": pk["hbm_gbs"], "hbm_source": pk["hbm_source"],
+                          "note": "node + triangle bytes a ray touches: served by L1 / L2 (the BVH is cache resident, DRAM traffic is `traffic`), "
+                                  "so set against the measured L2-resident copy bandwidth, not HBM"}
+    if out["traffic"]:
+        out["hbm"] = {"achieved": out["traffic"] / sec / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                      "frac": out["traffic"] / sec / 1e9 / pk["hbm_gbs"]}
+    return out
+
+
+def measure_config(pkg, torch, name, w, h, flush, pk, threads, with_cpu):
+    """One of the other BASELINE.json configs on this GPU: kernel ms (median, L2 flushed), Mrays/s, end to end into a
+    pinned canvas, first frame, and the oracle on the same whole frame."""
+    import numpy as np
+    text, assets = scene_source(name)
+    t0 = time.perf_counter()
+    info = pkg.parse_scene(text, assets, w, h)
+    setup = time.perf_counter() - t0
+    cam, wld = info.camera, info.world
+    buf = torch.empty((h, w, 3), dtype=torch.float64, device="cuda")
+    times, st, first = [], None, None
+    for i in range(6 + 7):  # the library measures its kernel candidates on the first five frames of a whole frame
+        flush.zero_()
+        torch.cuda.synchronize()
+        st = cam.render_device(wld, buf.data_ptr(), DEPTH)
+        if i == 0:
+            first = st.kernel_ms
+        if i >= 6:
+            times.append(st.kernel_ms)
+    times.sort()
+    ms = times[len(times) // 2]
+    host = pkg.pinned_empty((h, w, 3))
+    for _ in range(2):
+        cam.render(wld, DEPTH, None, out=host)
+    torch.cuda.synchronize()
+    e0 = time.perf_counter()
+    for _ in range(5):
+        cam.render(wld, DEPTH, None, out=host)
+    e_ms = (time.perf_counter() - e0) / 5 * 1e3
+    rays = st.rays
+    out = {"scene": "scenes/%s.json" % name, "width": w, "height": h, "kernel_ms": ms, "first_frame_ms": first,
+           "Mrays_s": rays / ms / 1e3, "rays_per_frame": rays,
+           "kernel": ("megakernel", "wavefront", "megakernel, several lanes per pixel")[st.kernel],
+           "e2e_ms": e_ms, "e2e_Mrays_s": rays / e_ms / 1e3, "d2h_bytes_per_step": h * w * 24, "scene_setup_s": setup}
+    rps = rays / (ms * 1e-3)
+    if name in CFG_FLOPS:
+        a = CFG_FLOPS[name] * rps / 1e12
+        out["roofline"] = {"bound": "issue", "alu": {"flops_per_ray": CFG_FLOPS[name], "achieved": a, "peak": pk["fp64_tflops"],
+                                                     "unit": "TFLOP/s (f64)", "frac": a / pk["fp64_tflops"]}}
+    elif name in CFG_BYTES:
+        a = CFG_BYTES[name] * rps / 1e9
+        out["roofline"] = {"bound": "issue", "model_bytes": {"bytes_per_ray": CFG_BYTES[name], "achieved": a, "unit": "GB/s",
+                                                             "peak_l2": pk["l2_gbs"], "frac_of_l2": a / pk["l2_gbs"]}}
+    if with_cpu:
+        r, s, desc, sc = cpu_frame(name, w, h, threads)
+        sc.close()
+        out["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": desc,
+                               "frame_s": s}
+        assert r == rays, "ray counts of GPU and oracle differ on %s" % name
+    pkg.free_pinned(host)
+    wld.close()
+    return out
+
+
 def main():
     quiet_stdout()
     ap = argparse.ArgumentParser()
@@ -203,6 +289,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the other BASELINE.json configs (N = 1 only)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "gather"],
                     help="N > 1: how the framebuffer reaches rank 0")
     args = ap.parse_args()
@@ -222,31 +309,50 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
 
-    text, assets = scene_source()
+    # ---- the scene: parsed ONCE (rank 0), broadcast, uploaded -------------------------------------------------
     t0 = time.perf_counter()
-    blob, cam = pkg.load_blob(text, assets, WIDTH, HEIGHT)
+    blob = cam = None
+    if rank == 0:
+        text, assets = scene_source()
+        blob, cam = pkg.load_blob(text, assets, WIDTH, HEIGHT)
     t1 = time.perf_counter()
+    if world > 1:
+        blob, cam = mg.broadcast_scene(blob, cam, rank, dev)
+    t1b = time.perf_counter()
     wld = pkg.World(blob, local_rank)
     torch.cuda.synchronize()
     t2 = time.perf_counter()
     camera = pkg.Camera(cam)
-    part = (TILE_ROWS, rank, world)
-    rows = camera.partition_rows(part)
-    mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
+    info = pkg.inspect_blob(blob) if rank == 0 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    # N > 1: every rank's kernel stores its tiles straight into rank 0's canvas over NVLink (PeerFrame);
-    # if symmetric memory cannot be set up on this box, packed rows + one NCCL gather (GatherFrame).
-    peer = gather = None
+
+    # ---- the process's very first launch (rank 0): CUDA loads the kernel image, the context is finished ... once per
+    #      process, not per scene (main.zig renders its 14 scenes in one process)
+    process_first_launch_ms = None
+    if rank == 0:
+        tiny = pkg.parse_scene(__import__("tests.scenes", fromlist=["x"]).SMOKE_SCENE, "", 64, 48, device=local_rank)
+        c0 = time.perf_counter()
+        tiny.camera.render(tiny.world)
+        process_first_launch_ms = 1e3 * (time.perf_counter() - c0)
+        tiny.world.close()
+
+    # ---- N > 1: who renders what, and how the frame reaches rank 0 --------------------------------------------
+    part = (TILE_ROWS, rank, world)
+    peer = gather = share = None
     exchange = "none (1 GPU)"
     if world > 1 and args.exchange != "gather":
         try:
             peer = mg.PeerFrame(WIDTH, HEIGHT, rank, world, dev)
-            exchange = "peer stores into rank 0's frame (symmetric memory over NVLink) + device barrier"
+            share = mg.TileShare(wld, WIDTH, HEIGHT, rank, world, dev, pkg)
+            exchange = ("tiles dealt by last frame's cost (peer-written cost buffers), pixels stored straight into rank 0's frame "
+                        "(symmetric memory over NVLink), one device barrier per frame")
         except Exception as e:  # noqa: BLE001
             if args.exchange == "peer":
                 raise
+            peer = share = None
             if rank == 0:
                 print("bench: symmetric memory unavailable (%s); falling back to NCCL gather" % e, file=sys.stderr)
     if peer is None:
@@ -255,27 +361,106 @@ def main():
             exchange = "packed rows + NCCL gather to rank 0 + de-interleave"
 
     def step_device():
+        """One frame, put on the stream (no host synchronisation): statistics are fetched later."""
         if peer is not None:
-            st = camera.render_device_frame(wld, peer.root_ptr, DEPTH, part, stream)
+            camera.render_device_async(wld, peer.root_ptr, DEPTH, None, stream)
             peer.finish()
-            return st
-        st = camera.render_device(wld, gather.local_ptr(), DEPTH, part, stream)
-        gather.assemble()
-        return st
+        elif world == 1:
+            camera.render_device_async(wld, gather.local_ptr(), DEPTH, None, stream)
+        else:
+            camera.render_device(wld, gather.local_ptr(), DEPTH, part, stream)
+            gather.assemble()
 
     def frame_on_rank0():
         return peer.frame if peer is not None else (gather.frame if world > 1 else gather.local)
 
-    # the caller-owned canvas of the e2e leg: page-locked (rtc_host_alloc, what the Zig shim uses), so the kernel
-    # stores pixels straight into host memory; a pageable canvas (staging frame + cudaMemcpy) is timed beside it
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def drain():
+        if peer is not None or world == 1:
+            return wld.fetch_stats()
+        return []
+
+    # ---- warm-up (untimed) ---------------------------------------------------------------------------------
+    for _ in range(max(args.warmup, 12)):  # the library measures its kernel candidates on the first five to eleven frames
+        step_device()
+        drain()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    stats = []
+    wall0 = time.perf_counter()
+    barrier()
+    for i in range(args.steps):
+        flush.zero_()
+        ev[i][0].record()
+        step_device()
+        ev[i][1].record()
+        if (i + 1) % 12 == 0:
+            stats += drain()
+    stats += drain()
+    barrier()
+    wall = time.perf_counter() - wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    if gather is not None and world > 1:  # fallback path: synchronous calls, statistics from a last frame
+        st = camera.render_device(wld, gather.local_ptr(), DEPTH, part, stream)
+        stats = [st] * args.steps
+    assert len(stats) == args.steps, "frames lost: %d statistics for %d steps" % (len(stats), args.steps)
+    rays = sum(s.rays for s in stats)
+    culled = sum(s.shadow_rays_culled for s in stats)
+    kernel_ms = sum(s.kernel_ms for s in stats)
+    launches = sum(s.launches for s in stats)
+
+    # the N-rank frame is the one-rank frame, bit for bit (rank 0 renders it alone into a second buffer)
+    if world > 1:
+        barrier()
+        if rank == 0:
+            alone = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, device=dev)
+            w1 = pkg.World(blob, local_rank)
+            camera.render_device(w1, alone.data_ptr(), DEPTH)
+            torch.cuda.synchronize()
+            assert torch.equal(alone, frame_on_rank0()), "the frame assembled from %d ranks differs from the one-GPU frame" % world
+            w1.close()
+            del alone
+        barrier()
+
+    # ---- cold numbers (rank 0): the first frame of a freshly created scene -- no tile order, the kernel guessed not
+    #      measured, the scene not in L2 (what main.zig's one frame per scene sees) -- and the frame after it
+    first_frame = None
+    if rank == 0:
+        cold = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.float64, device=dev)
+        c_setup = time.perf_counter()
+        w2 = pkg.World(blob, local_rank)
+        c_setup = time.perf_counter() - c_setup
+        flush.zero_()
+        torch.cuda.synchronize()
+        c0 = time.perf_counter()
+        st0 = camera.render_device(w2, cold.data_ptr(), DEPTH)
+        c_wall = 1e3 * (time.perf_counter() - c0)
+        flush.zero_()
+        torch.cuda.synchronize()
+        st1 = camera.render_device(w2, cold.data_ptr(), DEPTH)
+        first_frame = {"first_frame_ms": st0.kernel_ms, "first_frame_wall_ms": c_wall, "second_frame_ms": st1.kernel_ms,
+                       "kernel": ("megakernel", "wavefront", "megakernel, several lanes per pixel")[st0.kernel],
+                       "scene_create_s": c_setup,
+                       "note": "first frame of a freshly created scene: no tile order, the kernel guessed not measured, "
+                               "scene not yet in L2 (what main.zig's one frame per scene would see); kernel_ms of the steady state is `kernel_ms`"}
+        w2.close()
+        del cold
+
+    # ---- e2e leg (host buffers, D2H inside the timed region), wall clock bracketed by synchronize -------------
     host = pkg.pinned_empty((HEIGHT, WIDTH, 3))
     host_pageable = np.zeros((HEIGHT, WIDTH, 3), dtype=np.float64)
-
-    # N > 1: the host canvas is ONE shared-memory segment that every rank maps and page-locks; each rank's public
-    # Camera.render(world, partition) stores its rows into it over its own PCIe link (multi_gpu.SharedHostFrame).
-    # Fallback (registration refused): assemble on rank 0's GPU as in step_device, then one copy to pinned memory.
     shared = pinned = None
+    e2e_world = wld
     if world > 1:
+        # the e2e leg uses fixed row partitions (each rank's public Camera.render(world, partition) into one shared,
+        # page-locked host canvas over its own PCIe link): a scene of its own, without the tile sharing
+        e2e_world = pkg.World(blob, local_rank)
         ok = torch.zeros(1, device=dev)
         try:
             shared = mg.SharedHostFrame(WIDTH, HEIGHT, rank, world)
@@ -293,52 +478,26 @@ def main():
         if world == 1:  # the public call: Camera.render(world) -> host Canvas
             return camera.render(wld, DEPTH, None, out=host if canvas is None else canvas).stats
         if shared is not None:  # the same public call on every rank, rows of its partition, then a barrier
-            st = camera.render(wld, DEPTH, part, out=shared.array).stats
+            st = camera.render(e2e_world, DEPTH, part, out=shared.array).stats
             dist.barrier()
             return st
-        st = step_device()  # render + exchange on the GPUs, then the assembled frame goes to the host on rank 0
+        step_device()  # render + exchange on the GPUs, then the assembled frame goes to the host on rank 0
+        st = (drain() or [None])[-1]
         if rank == 0:
             pinned.copy_(frame_on_rank0(), non_blocking=False)
         return st
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 6)):  # >= 6: the library measures its kernel candidates on the first four to six frames
-        step_device()
-    barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    rays = kernel_ms = culled = 0
-    launches = 0
-    wall0 = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()
-        barrier()
-        ev[i][0].record()
-        st = step_device()
-        ev[i][1].record()
-        rays += st.rays
-        culled += st.shadow_rays_culled
-        kernel_ms += st.kernel_ms
-        launches += st.launches
-    barrier()
-    wall = time.perf_counter() - wall0
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    # e2e leg (host buffers, D2H inside the timed region), wall clock bracketed by synchronize
-    for _ in range(2):
+    for _ in range(6 if world > 1 else 2):
         step_e2e()
     barrier()
     e0 = time.perf_counter()
     e_rays = 0
     for i in range(args.steps):
-        e_rays += step_e2e().rays
+        st = step_e2e()
+        e_rays += st.rays if st is not None else 0
     barrier()
     e_secs = time.perf_counter() - e0
-    p_secs = None
+    p_secs = r8_secs = None
     if world == 1:
         step_e2e(host_pageable)
         barrier()
@@ -348,8 +507,23 @@ def main():
         barrier()
         p_secs = time.perf_counter() - p0
         assert np.array_equal(host, host_pageable), "pinned and pageable canvases differ"
+        # the lib.zig twin: RGBA8 into a pinned buffer (what the Renderer's pixel buffer is), 4 B per pixel over PCIe
+        import ctypes
+        rgba = pkg.pinned_empty((HEIGHT, WIDTH, 4), dtype=np.uint8)
+        st8 = pkg.rtc_stats()
+
+        def step_rgba8():
+            pkg._check(pkg.lib().rtc_render_rgba8(wld._h, ctypes.byref(camera.c), DEPTH, None, rgba.ctypes.data, ctypes.byref(st8)))
+        for _ in range(2):
+            step_rgba8()
+        barrier()
+        r0 = time.perf_counter()
+        for i in range(args.steps):
+            step_rgba8()
+        barrier()
+        r8_secs = time.perf_counter() - r0
+        assert np.array_equal(rgba[..., :3], pkg.Canvas(host).to_image()), "RGBA8 frame is not clamp() of the f64 frame"
     if shared is not None:
-        step_device()
         barrier()
         if rank == 0:  # the host canvas written by N ranks over N links == the frame assembled on rank 0's GPU
             assert np.array_equal(shared.array, frame_on_rank0().cpu().numpy()), "shared host canvas differs from the device frame"
@@ -370,24 +544,27 @@ def main():
             torch.cuda.synchronize()
             best = min(best, c0.elapsed_time(c1))
         d2h_ms = best
+        del src, dst
 
+    k_mine = kernel_ms / args.steps
     t = torch.tensor([dev_ms, e_secs], dtype=torch.float64, device=dev)
     tot = torch.tensor([float(rays), float(e_rays), float(launches)], dtype=torch.float64, device=dev)
+    k_all = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_gather(k_all, torch.tensor([k_mine], dtype=torch.float64, device=dev))
+    else:
+        k_all[0][0] = k_mine
     dev_ms, e_secs = float(t[0]), float(t[1])
     rays_all, e_rays_all, launches_all = float(tot[0]), float(tot[1]), int(tot[2])
+    k_ranks = [float(k[0]) for k in k_all]
 
     if shared is not None:
         shared.close()
     if rank == 0:
-        peak, which = peaks()
+        pk = measured_peaks()
         value = rays_all / (dev_ms * 1e-3) / 1e6
-        # roofline of the render kernel on THIS rank: algorithmic bytes per launch / mean launch time
-        k_ms = kernel_ms / args.steps
-        achieved = (rays / args.steps) * BYTES_PER_RAY / (k_ms * 1e-3) / 1e9
-        traffic, traffic_src = ncu_traffic()
         line = base_line(args, world)
         line.update({
             "value": value, "ms_per_step": dev_ms / args.steps,
@@ -408,26 +585,46 @@ def main():
             # shadow rays the reference casts (and `value` counts) but this renderer does not trace because the
             # light is behind the surface: the result is ambient either way (material.zig:55-63); rank 0's share
             "shadow_rays_culled_per_frame": culled / args.steps,
-            "kernel_ms": k_ms,
+            "kernel_ms": max(k_ranks),
+            "kernel_ms_per_rank": {"min": min(k_ranks), "max": max(k_ranks), "all": k_ranks,
+                                   "note": "CUDA-event time of each rank's render kernel (+ order kernels when an order is made), mean over the steps"},
+            "sync_overhead_ms": dev_ms / args.steps - max(k_ranks),
             "wall_s_timed_region": wall,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": which + " (MEASURED_PEAKS.json hbm_gbs)",
-                         "model": "%d algorithmic B/ray (SURVEY.md 8d) x rays per launch / CUDA-event launch time; the "
-                                  "working set is L2-resident (traffic = measured DRAM bytes per launch: ~1 %% of the "
-                                  "algorithmic bytes), so this is a node-fetch figure set against the HBM peak and may "
-                                  "exceed it; frac_of_l2_copy sets it against the measured L2-resident copy bandwidth" % BYTES_PER_RAY,
-                         **l2_fraction(achieved)},
+            "roofline": roofline_block(rays / args.steps, k_mine, pk),
             "clocks": sampler.summary(),
             "exchange": exchange,
-            "scene_setup": {"parse_flatten_s": t1 - t0, "bvh_build_upload_s": t2 - t1, "blob_bytes": len(blob)},
+            "scene_setup": {"parse_flatten_s": t1 - t0, "broadcast_s": t1b - t1, "bvh_build_upload_s": t2 - t1b,
+                            "blob_bytes": len(blob), "parsed_on": "rank 0 only" if world > 1 else "this process",
+                            "scene": info.as_dict() if info is not None else None},
         })
+        if first_frame:
+            line["first_frame"] = first_frame
+            line["first_frame_ms"] = first_frame["first_frame_ms"]
+            line["cold_first_frame_s"] = (t2 - t0) + first_frame["first_frame_wall_ms"] * 1e-3
+            line["cold_first_frame"] = "parse + flatten + BVH build + upload + the first frame into device memory (scene_setup + first_frame); the once-per-process CUDA start-up is process_first_launch_ms"
+            line["process_first_launch_ms"] = process_first_launch_ms
+        if r8_secs:
+            line["e2e_rgba8"] = {"value": rays_all / r8_secs / 1e6, "unit": "Mrays/s",
+                                 "ms_per_step": 1e3 * r8_secs / args.steps, "d2h_bytes_per_step": int(HEIGHT * WIDTH * 4),
+                                 "call": "rtc_render_rgba8 (lib.zig:135-155 twin) into a pinned buffer: the kernel stores clamp()ed "
+                                         "pixels straight into host memory"}
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            r, s, desc = cpu_sample(threads)
+            r, s, desc, sc = cpu_frame(SCENE, WIDTH, HEIGHT, threads)
+            sc.close()
             line["cpu_baseline"] = {"value": r / s / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-                                    "sample": desc}
+                                    "sample": desc, "frame_s": s}
+        if world == 1 and not args.no_configs:
+            threads = os.cpu_count() or 1
+            line["configs"] = {}
+            for key, name, w, h in CONFIGS:
+                try:
+                    line["configs"][key] = measure_config(pkg, torch, name, w, h, flush, pk, threads, not args.no_cpu_baseline)
+                except Exception as e:  # noqa: BLE001
+                    line["configs"][key] = {"error": str(e)}
         emit(line)
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -117,6 +117,25 @@ int rtc_render_device_frame(rtc_scene* scene, const rtc_camera* cam, int max_dep
 int rtc_render_device_async(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                             double* d_frame, void* stream);
 int rtc_stats_fetch(rtc_scene* scene, rtc_stats* stats_out, uint32_t max_frames, uint32_t* n_out);
+/* One frame shared by several renderers, one PROCESS per GPU (rank r of n_ranks; the layout torchrun / MPI hosts use).
+ * Instead of fixed row partitions the renderers take the tiles of ONE order -- the frame's 8x4-pixel tiles sorted into
+ * buckets by what they cost in the previous frame -- in turn: entry r, r + n, r + 2n, ...: every renderer gets its
+ * share of the expensive tiles.  To make that order, every renderer needs every tile's cost: each adds the cost of the
+ * tiles it renders to the buffers of ALL renderers (cost[b][r] = buffer b of renderer r as the calling device
+ * addresses it: peer-mapped / symmetric memory over NVLink; two buffers per renderer, `words` 32-bit words each,
+ * >= rtc_tile_share_words(hsize, vsize), allocated by the caller).
+ * Protocol: (1) every rank calls rtc_scene_share_tiles, then a barrier; (2) every rank renders frame k with
+ * rtc_render_device_frame / rtc_render_device_async(part = NULL, d_frame = the shared whole frame); (3) a device-side
+ * barrier across the ranks on the streams used (it is also what tells rank 0 that the frame is complete) -- then frame
+ * k + 1.  Without (3) the renderers' copies of the costs can differ and tiles can be rendered twice or not at all.
+ * rtc_scene_share_tiles(scene, NULL) ends the sharing. */
+typedef struct rtc_tile_share {
+    uint32_t rank, n_ranks; /* n_ranks <= 8 */
+    uint64_t words;
+    void* cost[2][8];
+} rtc_tile_share;
+uint64_t rtc_tile_share_words(uint64_t hsize, uint64_t vsize);
+int rtc_scene_share_tiles(rtc_scene* scene, const rtc_tile_share* share);
 uint64_t rtc_partition_rows(uint64_t vsize, const rtc_partition* part);
 
 /* Host loader: the C++ mirror of src/parsing (scene.zig:612, obj.zig:195) + flattener, for hosts

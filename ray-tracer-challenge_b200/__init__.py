@@ -49,6 +49,11 @@ class rtc_scene_info(ctypes.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
+class rtc_tile_share(ctypes.Structure):
+    _fields_ = [("rank", ctypes.c_uint32), ("n_ranks", ctypes.c_uint32), ("words", ctypes.c_uint64),
+                ("cost", (ctypes.c_void_p * 8) * 2)]
+
+
 class rtc_stats(ctypes.Structure):
     _fields_ = [("primary_rays", ctypes.c_uint64), ("shadow_rays", ctypes.c_uint64),
                 ("secondary_rays", ctypes.c_uint64), ("pixels", ctypes.c_uint64), ("kernel_ms", ctypes.c_float),
@@ -65,7 +70,7 @@ class rtc_stats(ctypes.Structure):
 
 
 # every symbol include/rtc_b200.h declares
-EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_set_devices", "rtc_render_device_async", "rtc_stats_fetch", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
+EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_set_devices", "rtc_render_device_async", "rtc_stats_fetch", "rtc_tile_share_words", "rtc_scene_share_tiles", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
            "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png"]
 # include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
@@ -88,9 +93,14 @@ def lib():
     L.rtc_last_error.restype = cp
     L.rtc_device_count.restype = ctypes.c_int
     L.rtc_set_device.argtypes = [ctypes.c_int]
+    if not hasattr(L, "rtc_set_devices"):  # an older build of the library (tools/kernel_variants.py compares against one)
+        return _finish_old(L)
     L.rtc_set_devices.argtypes = [ctypes.c_int]
     L.rtc_render_device_async.argtypes = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, ctypes.POINTER(rtc_partition), vp, vp]
     L.rtc_stats_fetch.argtypes = [vp, ctypes.POINTER(rtc_stats), ctypes.c_uint32, ctypes.POINTER(ctypes.c_uint32)]
+    L.rtc_tile_share_words.argtypes = [ctypes.c_uint64, ctypes.c_uint64]
+    L.rtc_tile_share_words.restype = ctypes.c_uint64
+    L.rtc_scene_share_tiles.argtypes = [vp, ctypes.POINTER(rtc_tile_share)]
     L.rtc_blob_inspect.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(rtc_scene_info)]
     L.rtc_scene_create.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
     L.rtc_scene_destroy.argtypes = [vp]
@@ -129,6 +139,25 @@ def lib():
     L.rtcRendererSetAssetDir.argtypes = [cp]
     L.rtcRendererSetAssetDir.restype = None
     L.rtcRendererLastStats.argtypes = [ctypes.POINTER(rtc_stats)]
+    _lib = L
+    return L
+
+
+def _finish_old(L):
+    """Bindings of a round-1 build: the entry points both rounds have (enough for tools/bench_all.py)."""
+    global _lib
+    vp, cp = ctypes.c_void_p, ctypes.c_char_p
+    L.rtc_scene_create.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
+    L.rtc_scene_destroy.argtypes = [vp]
+    L.rtc_scene_destroy.restype = None
+    common = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, ctypes.POINTER(rtc_partition)]
+    L.rtc_render_device.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_render_device_frame.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_load_scene_json.argtypes = [cp, cp, ctypes.c_long, ctypes.c_long, ctypes.POINTER(vp),
+                                      ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(rtc_camera)]
+    L.rtc_blob_free.argtypes = [vp]
+    L.rtc_blob_free.restype = None
+    L.rtc_set_devices = lambda n: 0
     _lib = L
     return L
 
@@ -243,6 +272,18 @@ class World:
             _check(L.rtc_scene_create(blob, len(blob), ctypes.byref(self._h)))
         finally:
             L.rtc_set_devices(1)
+
+    def share_tiles(self, rank, n_ranks, words, cost_ptrs):
+        """rtc_scene_share_tiles: cost_ptrs[b][r] = device address (int) of buffer b of renderer r.  n_ranks <= 1 ends it."""
+        if n_ranks <= 1:
+            _check(lib().rtc_scene_share_tiles(self._h, None))
+            return
+        sh = rtc_tile_share()
+        sh.rank, sh.n_ranks, sh.words = rank, n_ranks, words
+        for b in range(2):
+            for r in range(n_ranks):
+                sh.cost[b][r] = cost_ptrs[b][r]
+        _check(lib().rtc_scene_share_tiles(self._h, ctypes.byref(sh)))
 
     def fetch_stats(self, max_frames=16):
         """Waits for the frames put on a stream by Camera.render_device_async and returns their rtc_stats, oldest first."""

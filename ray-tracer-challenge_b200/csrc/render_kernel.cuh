@@ -107,7 +107,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     // whose chains of dependent trips set the time of a small partition get the short chain; the rest of the frame
     // is not traced twice.
     constexpr bool MIXED = LPP == 0;
-    const unsigned long long heavy_items = MIXED && P.tile_order ? (unsigned long long)__ldg(P.heavy_tiles) * 128ull : 0ull;
+    // (of the heavy tiles at the head of the order this renderer is dealt its runs, like of all others)
+    unsigned long long heavy_items = 0ull;
+    if (MIXED && P.tile_order) {
+        const unsigned h = __ldg(P.heavy_tiles), run = 1u << P.deal_shift, round = run * P.deal_n;
+        const unsigned rem = h % round, lo = P.deal_rank * run;
+        heavy_items = (unsigned long long)(h / round * run + (rem > lo ? min(rem - lo, run) : 0u)) * 128ull;
+    }
     const unsigned long long n_items = P.n_items + heavy_items / 4 * 3;  // a heavy tile is 128 lane items instead of 32
     int lpp = MIXED ? 1 : LPP;  // lanes per pixel of the tile this warp is working on
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
@@ -176,13 +182,16 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
 #endif
         if (need) {
             // cost of the tile this warp is through with (clock ticks / 64), for the order of the NEXT frame
-            if (P.tile_cost && lane == 0 && PK(PK_SPARE) >= 0.0) {
+            // (added to the cost arrays of all renderers sharing the frame, so that all copies stay equal)
+            if (P.cost_peer[0] && lane == 0 && PK(PK_SPARE) >= 0.0) {
                 const long long t0 = __double_as_longlong(PK(PK_SPARE + 1));
                 const unsigned cost = (unsigned)((clock64() - t0) >> 6);
-                atomicAdd(P.tile_cost + (unsigned)PK(PK_SPARE), cost);
-#ifndef RTC_TRIP_PROBE
-                atomicAdd(P.counters + 6, (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
-#endif
+                const unsigned done_tile = (unsigned)PK(PK_SPARE);
+                for (unsigned r = 0; r < P.deal_n; r++) {
+                    unsigned* cp = P.cost_peer[r];
+                    atomicAdd(cp + done_tile, cost);
+                    atomicAdd(reinterpret_cast<unsigned long long*>(cp + P.cost_tiles), (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
+                }
                 PK(PK_SPARE) = -1.0;
             }
             unsigned long long base = 0;
@@ -204,10 +213,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     } else {
                         pitem = item / (unsigned)LPP;
                     }
-                    unsigned long long tile = pitem >> 5;
+                    unsigned long long tile = ((((unsigned)(pitem >> 5) >> P.deal_shift) * P.deal_n + P.deal_rank) << P.deal_shift) |
+                                              ((unsigned)(pitem >> 5) & ((1u << P.deal_shift) - 1u));  // the entry of the order this renderer is dealt
                     unsigned in = (unsigned)(pitem & 31u);
                     if (P.tile_order) tile = __ldg(P.tile_order + tile);  // most expensive tiles of the last frame first
-                    if (P.tile_cost && lane == 0) {
+                    if (P.cost_peer[0] && lane == 0) {
                         PK(PK_SPARE) = (double)tile;
                         PK(PK_SPARE + 1) = __longlong_as_double(clock64());
                     }
@@ -258,7 +268,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 q.t = RTC_INF;
                 q.leaf = -1;
                 q.a = q.b = 0.0;
-                q.c_leaf = 0;
+                q.c_leaf = -1;
             } else if (state == ST_SHADOW) {  // World.isShadowed (world.zig:126-135)
                 // over_point = point + normal * EPSILON, recomputed from the parked ray and hit
                 // (same operations as PreComputations.new, world.zig:219-224: same bits)
@@ -328,7 +338,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 const double* nrm = nullptr;
                 if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
                     nrm = S.normals[L.triangle].n;
-                    if (!LEAN && kind == RTC_SMOOTH_TRIANGLE && !q.c_leaf) {
+                    if (!LEAN && kind == RTC_SMOOTH_TRIANGLE && q.c_leaf != hit_leaf) {
                         // u,v of a smooth triangle that is a CSG operand: same ray, same test, same values
                         const rtc_triangle& T = S.blob_tris[L.triangle];
                         double tt;

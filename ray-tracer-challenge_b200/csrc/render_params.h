@@ -19,8 +19,19 @@ namespace rtc {
 #define RTC_TILE_W (1u << RTC_TILE_W_LOG2)
 #define RTC_TILE_H (1u << RTC_TILE_H_LOG2)
 
-#define RTC_PARK_SLOTS 27  // doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*), mailbox included
-#define RTC_MAILBOX_SLOTS 5  // rt_trace.cuh MB_SLOTS (the wavefront kernels keep only these in shared memory)
+#define RTC_MAX_SHARE 8    // renderers (GPUs) that can share one frame tile by tile (RenderParams::cost_peer)
+// Work sharing inside the mesh traversal (rt_trace.cuh trace_meshes): built, measured slower on B200, off by default.
+#ifndef RTC_STEAL
+#define RTC_STEAL 0
+#endif
+#if RTC_STEAL
+#define RTC_MAILBOX_SLOTS 5  // rt_trace.cuh MB_SLOTS: per-lane mailbox in shared memory
+#else
+#define RTC_MAILBOX_SLOTS 0
+#endif
+// doubles of per-lane state parked in shared memory (render_kernel.cuh PK_*), mailbox included.  Shared memory is taken
+// out of the L1 cache the BVH nodes live in: every kilobyte counts (27 slots instead of 22 cost teapot.json 5 %).
+#define RTC_PARK_SLOTS (22 + RTC_MAILBOX_SLOTS)
 
 struct DCamera {  // Camera(T) fields read by rayForPixel (camera.zig:22-30)
     unsigned long long hsize, vsize;
@@ -48,9 +59,18 @@ struct RenderParams {
     // of this partition, the most expensive ones of the previous frame first (rtc_api.cu).  tile_cost[tile] receives
     // the time the warps spent on the tile in this frame (NULL: not recorded).
     const unsigned int* tile_order;
-    unsigned int* tile_cost;
+    // Cost recording: cost_peer[0] = this renderer's array (NULL: not recorded); entry [cost_tiles] (8-byte aligned, two
+    // words) receives the sum of all costs.  Several renderers sharing one frame (one per GPU; deal_n of them, this one
+    // is deal_rank) take the entries deal_rank, deal_rank + deal_n, ... of the SAME order -- the tiles of every cost
+    // bucket are dealt round -- and add the cost of each tile they render to the arrays of ALL of them (cost_peer[r] =
+    // renderer r's array as this device addresses it: peer memory over NVLink), so that each can make the same next
+    // order from its own copy.  deal_n == 1: a renderer by itself.
+    unsigned int* cost_peer[RTC_MAX_SHARE];
+    unsigned int cost_tiles;
+    unsigned int deal_n, deal_rank;
+    unsigned int deal_shift;  // the order is dealt in runs of 1 << deal_shift consecutive entries (neighbouring tiles stay with one renderer)
     const unsigned int* heavy_tiles;  // device word: how many leading entries of tile_order cost >= 8x the mean (LPP == 0)
-    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays, [6] sum of tile_cost
+    unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };
 
 // ---- wavefront path (render_wavefront.cuh) ------------------------------------------------------------

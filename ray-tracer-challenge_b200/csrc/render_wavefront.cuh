@@ -196,7 +196,7 @@ wave_kernel(DScene S, WaveParams W) {
             q.t = RTC_INF;
             q.leaf = -1;
             q.a = q.b = 0.0;
-            q.c_leaf = 0;  // Q_CLOSEST: q.a / q.b hold the u,v of the hit triangle
+            q.c_leaf = -1;  // Q_CLOSEST: the leaf whose u,v are in q.a / q.b
             q.flag = 0;
             wf_trace<MESH>(q, S, stack, &err, live);
 
@@ -217,7 +217,7 @@ wave_kernel(DScene S, WaveParams W) {
                 const double* nrm = nullptr;
                 if (kind == RTC_TRIANGLE || kind == RTC_SMOOTH_TRIANGLE) {
                     nrm = S.normals[L.triangle].n;
-                    if (kind == RTC_SMOOTH_TRIANGLE && !q.c_leaf) {
+                    if (kind == RTC_SMOOTH_TRIANGLE && q.c_leaf != hit_leaf) {
                         // u,v of a smooth triangle that is a CSG operand: same ray, same test, same values
                         const rtc_triangle& T = S.blob_tris[L.triangle];
                         double tt;

@@ -24,7 +24,7 @@ enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8, ERR
 
 // One world query.  The three modes never coexist, so they share their fields:
 //                 t                 leaf        a       b            c_leaf      flag
-//   Q_CLOSEST     best t so far     best leaf   u       v            u,v valid   -
+//   Q_CLOSEST     best t so far     best leaf   u       v            leaf u,v are of   -
 //   Q_SHADOW      light distance    -           -       -            -           shadowed
 //   Q_CONTAINERS  t of the hit      hit leaf    c_t     hit_last_t   c_leaf      hit_odd
 // In every mode nothing beyond t can change the result: t is the far end of the useful range.
@@ -131,7 +131,6 @@ __device__ __forceinline__ void accept(Query& q, const DScene& S, int leaf, uint
             if (t >= 0.0 && (t < q.t || (t == q.t && leaf < q.leaf))) {
                 q.t = t;
                 q.leaf = leaf;
-                q.c_leaf = 0;  // not a triangle whose u,v are in q.a / q.b (trace_prim sets it for a stray triangle)
             }
         }
     } else if (q.mode == Q_SHADOW) {
@@ -196,7 +195,7 @@ __device__ __forceinline__ void trace_prim(Query& q, const DScene& S, int i) {
         if (q.mode == Q_CLOSEST && (q.t != t_before || q.leaf != leaf_before)) {  // this triangle is the new closest hit
             q.a = u;
             q.b = v;
-            q.c_leaf = 1;
+            q.c_leaf = leaf_id;  // whose u,v these are (the shading stage recomputes them for any other smooth triangle)
         }
         return;
     }
@@ -224,7 +223,7 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
                     q.leaf = leaf;
                     q.a = u;
                     q.b = v;
-                    q.c_leaf = 1;  // u,v valid
+                    q.c_leaf = leaf;  // whose u,v these are
                 }
             }
         } else if (q.mode == Q_SHADOW) {
@@ -234,6 +233,21 @@ __device__ __forceinline__ void mesh_tris(Query& q, const DScene& S, int first, 
         }
     }
 }
+
+// Work sharing inside the mesh traversal (trace_meshes, below).
+// MEASURED on B200 (profiles/README.md, round 2): correct (frames and ray counts bit-identical, 70 GPU tests green) and
+// it does raise the lanes active per instruction of this loop (10.5 -> 14.1), but the frame gets SLOWER -- dragons.json
+// 1080p 0.87 -> 1.24 ms, teapot 0.66 -> 0.82, a 1/8 partition 0.27 -> 0.35 -- and stays slower when helping is made
+// rare (only shadow queries, only with >= 28 idle lanes and >= 2 pending entries: 1.14 ms): the warp executes MORE
+// instructions (578 M against 505 M: subtrees a closest-hit query would have culled, the bookkeeping at every step) and
+// the loop no longer fits the instruction cache (stall_no_instruction 1.0 -> 2.5 per issue; 52 bytes of spills).  This
+// kernel lives on a small, register-tight inner loop.  Off by default; -DRTC_STEAL=1 builds it.
+// (the default, RTC_STEAL 0, is set in render_params.h: the host sizes shared memory by it)
+#if RTC_STEAL
+#define RTC_STACK_BASE(T) ((T).sb)
+#else
+#define RTC_STACK_BASE(T) 0
+#endif
 
 // Mesh traversal state of one lane.  It lives across trips of the render loop (render.cu): a lane
 // whose query is finished leaves to be shaded and refilled while the others keep their place.
@@ -245,7 +259,9 @@ struct MeshTrav {
     int mbase;      // meshes [mbase, mbase + 32) are described by mask
     unsigned mask;  // candidate meshes not visited yet
     int node, sp;
+#if RTC_STEAL
     int sb;         // the lane's stack is [sb, sp): entries below sb were handed to other lanes (trace_meshes)
+#endif
     int lmap;       // DMesh.leaf_map of the mesh being traversed
     float t_hi;
     V3 oo, dd;  // the ray in the current mesh's object space
@@ -274,7 +290,9 @@ __device__ __forceinline__ void mesh_begin(const Query& q, const DScene& S, cons
     T.mask = mesh_mask(q, S, wr, 0);
     T.node = RTC_MESH_END;
     T.sp = 0;
+#if RTC_STEAL
     T.sb = 0;
+#endif
     T.t_hi = query_t_hi(q);
 }
 
@@ -333,7 +351,7 @@ __device__ __forceinline__ bool mesh_inner(const Query& q, const DScene& S, Mesh
                 node = c0;
             } else if (h1) {
                 node = c1;
-            } else if (sp > T.sb) {
+            } else if (sp > RTC_STACK_BASE(T)) {
                 sp--;
                 node = stack[sp * RTC_BLOCK];
             } else {
@@ -352,7 +370,7 @@ __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T
     mesh_tris(q, S, enc >> 3, enc & 7, T.oo, T.dd, S.mesh_leaf + T.lmap);
     if (q.mode == Q_SHADOW && q.flag) return false;
     if (q.mode == Q_CLOSEST) T.t_hi = fminf(T.t_hi, __double2float_ru(q.t));  // (T.t_hi may hold a tighter bound found by a helper)
-    if (T.sp > T.sb) {
+    if (T.sp > RTC_STACK_BASE(T)) {
         T.sp--;
         T.node = stack[T.sp * RTC_BLOCK];
     } else {
@@ -371,16 +389,6 @@ __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T
 // shared memory: closest hit = min over (t, leaf) -- associative, so the result is the same whoever finds what: exact;
 // shadow = any hit.  Bounds travel too: a hit found by anyone working for a query shrinks t_hi of all of them (one
 // shared-memory atomicMin per step), a shadow hit stops them.  Containers queries (parity of ALL hits) are not shared.
-// MEASURED on B200 (profiles/README.md, round 2): correct (frames and ray counts bit-identical, 70 GPU tests green) and
-// it does raise the lanes active per instruction of this loop (10.5 -> 14.1), but the frame gets SLOWER -- dragons.json
-// 1080p 0.87 -> 1.24 ms, teapot 0.66 -> 0.82, a 1/8 partition 0.27 -> 0.35 -- and stays slower when helping is made
-// rare (only shadow queries, only with >= 28 idle lanes and >= 2 pending entries: 1.14 ms): the warp executes MORE
-// instructions (578 M against 505 M: subtrees a closest-hit query would have culled, the bookkeeping at every step) and
-// the loop no longer fits the instruction cache (stall_no_instruction 1.0 -> 2.5 per issue; 52 bytes of spills).  This
-// kernel lives on a small, register-tight inner loop.  Off by default; -DRTC_STEAL=1 builds it.
-#ifndef RTC_STEAL
-#define RTC_STEAL 0
-#endif
 #ifndef RTC_STEAL_MIN_DEPTH
 #define RTC_STEAL_MIN_DEPTH 1  // pending entries a lane must have on its stack before it gives the bottom one away
 #endif
@@ -390,8 +398,8 @@ __device__ __forceinline__ bool mesh_leaf(Query& q, const DScene& S, MeshTrav& T
 #ifndef RTC_STEAL_MODES
 #define RTC_STEAL_MODES 3      // bit 0: shadow queries are shared, bit 1: closest-hit queries are shared
 #endif
-enum { MB_T = 0, MB_LF = 1, MB_U = 2, MB_V = 3, MB_BOUND = 4, MB_SLOTS = 5 };  // doubles per lane (stride RTC_BLOCK)
-#define RTC_UV_NONE 2  // Query::c_leaf of a helper that has not found anything yet
+enum { MB_T = 0, MB_LF = 1, MB_U = 2, MB_V = 3, MB_BOUND = 4, MB_SLOTS = RTC_MAILBOX_SLOTS };  // doubles per lane (stride RTC_BLOCK)
+#define RTC_UV_NONE (-2)  // Query::c_leaf of a helper that has not found anything yet
 
 // q, a finished Q_CLOSEST / Q_SHADOW task, merged into the mailbox of lane `tgt` (mbw = the warp's lane-0 column)
 __device__ __forceinline__ void mb_merge(double* mbw, int tgt, const Query& q) {
@@ -439,6 +447,16 @@ __device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, MeshTrav
         }
     };
 #endif
+#if !RTC_STEAL
+    while (__any_sync(FULL, busy)) {
+        if (busy) busy = mesh_inner(q, S, T, stack, err);
+        if (!__any_sync(FULL, busy)) break;
+        if (busy) busy = mesh_leaf(q, S, T, stack);
+    }
+    (void)mbw;
+    (void)own_live;
+    (void)lane;
+#else
     while (__any_sync(FULL, busy)) {
         if (busy) busy = mesh_inner(q, S, T, stack, err);
         bool at_leaf = busy;  // holding a leaf for mesh_leaf (a lane that takes over a subtree below holds an inner node)
@@ -550,10 +568,7 @@ __device__ __forceinline__ void trace_meshes(Query& q, const DScene& S, MeshTrav
         }
         __syncwarp();
     }
-#else
-    (void)mbw;
-    (void)own_live;
-    (void)lane;
+#endif
 #endif
 }
 
@@ -654,8 +669,7 @@ __device__ __forceinline__ void trace_csg(Query& q, const DScene& S, const DCsgR
             if (ts[i] >= 0.0) {
                 if (ts[i] < q.t || (ts[i] == q.t && ids[i] < q.leaf)) {
                     q.t = ts[i];
-                    q.leaf = ids[i];
-                    q.c_leaf = 0;  // a CSG operand: u,v of a smooth triangle are recomputed by the caller
+                    q.leaf = ids[i];  // (a smooth triangle as CSG operand: q.c_leaf != q.leaf, u,v are recomputed by the caller)
                 }
                 break;
             }

@@ -52,7 +52,7 @@ struct rtc_scene {
     struct Frame {
         int state = 0;  // 0 free, 1 on the stream, 2 statistics ready
         int best_slot = 0, lpp = 1, rc = 0;
-        bool lpt = false;
+        bool lpt = false, order_made = false, ordered = false;
         uint64_t pixels = 0;
         rtc_stats stats{};
     };
@@ -80,16 +80,87 @@ struct rtc_scene {
     // wavefront wins where pixels have long or branching ray trees, the megakernel where they do not and on
     // small frames): frames 1-4 alternate between the heuristic choice and the other kernel, later frames use the faster one.
     int frames = 0;
-    // [0] megakernel, [1] wavefront, [2] megakernel with four lanes per pixel on last frame's expensive tiles (small
-    // partitions only, see mixed_candidate); per pixel-count of the last frame
-    float best_ms[3] = {-1.0f, -1.0f, -1.0f};
+    // [0] megakernel, [1] wavefront, [2..4] megakernel with four lanes per pixel on the tiles that cost >= 8x / 4x / 2x the
+    // mean in the frame the order was made from (small partitions only, see mixed_candidate); per pixel-count of the last frame
+    float best_ms[5] = {-1.0f, -1.0f, -1.0f, -1.0f, -1.0f};
     size_t tuned_pixels = 0;
-    // tile order of the megakernel: cost of every tile in the last frame, and the permutation made from it
-    unsigned* d_tile_cost = nullptr;
+    // Tile order of the megakernel: frame k adds the cost of every tile to cost buffer k & 1; frame k + 1 first makes
+    // the permutation out of it (tile_order.cu), clears it for frame k + 2, then renders in that order.  Two buffers,
+    // because renderers sharing a frame (share.n > 1) write into EACH OTHER's buffers: the one a peer may already be
+    // filling for the next frame is never the one being read or cleared here (rtc_scene_share_tiles).
+    unsigned* d_cost_own[2] = {nullptr, nullptr};  // own allocations (unused when the caller provided shared buffers)
+    unsigned* d_scratch = nullptr;                 // bucket counts of tile_order.cu + the heavy-tile count
     unsigned* d_tile_order = nullptr;
-    size_t tile_cap = 0;      // tiles the two arrays hold
-    size_t order_tiles = 0;   // tiles the current permutation covers (0: none yet)
+    size_t tile_cap = 0;        // tiles the own cost buffers hold
+    size_t order_cap = 0;       // tiles d_scratch / d_tile_order hold
+    // A frame records costs only when the order at hand was not made from this very view (camera, depth, partition): a
+    // re-render of the same view keeps its order and pays nothing for it -- no cost atomics, no memset, no order kernels;
+    // a camera that moves records every frame and re-orders every frame.
+    struct View {
+        rtc_camera cam;
+        int depth;
+        unsigned tile_rows, part, n_parts, deal_rank, deal_n;
+    };
+    size_t pending = 0;         // tiles the last frame recorded costs for (0: none), in cost buffer (parity ^ 1)
+    View pending_view{};        // ... and the view it rendered
+    size_t order_tiles = 0;     // tiles d_tile_order is a permutation of (0: no order)
+    View order_view{};          // the view whose costs it was made from
+    int parity = 0;             // cost buffer the NEXT recording frame writes
+    struct Share {
+        unsigned rank = 0, n = 1;
+        unsigned* cost[2][RTC_MAX_SHARE] = {};  // [buffer][renderer], as THIS device addresses them
+        size_t words = 0;                       // capacity of each buffer
+        bool external = false;                  // buffers belong to the caller (rtc_scene_share_tiles)
+    } share;
 };
+
+// words of one cost buffer for n_tiles tiles: the costs, padded to an even count, then the 64-bit sum
+static size_t cost_words(size_t n_tiles) { return ((n_tiles + 1) & ~size_t(1)) + 2; }
+static size_t frame_tiles(uint64_t hsize, uint64_t rows) {
+    return (size_t)((hsize + RTC_TILE_W - 1) / RTC_TILE_W) * (size_t)((rows + RTC_TILE_H - 1) / RTC_TILE_H);
+}
+
+// The replicas of a scene (rtc_set_devices) share their frames tile by tile: cost buffers on every device, each
+// addressable from all others (peer access, all pairs).  Grown when a frame needs more tiles.
+static int ensure_replica_share(rtc_scene* s, size_t n_tiles) {
+    const unsigned n = 1u + (unsigned)s->replicas.size();
+    if (s->share.n == n && s->tile_cap >= n_tiles) return RTC_OK;
+    if (n > RTC_MAX_SHARE) return fail(RTC_ERR_INVALID, "more devices than renderers that can share a frame");
+    std::vector<rtc_scene*> all{s};
+    all.insert(all.end(), s->replicas.begin(), s->replicas.end());
+    const size_t words = cost_words(n_tiles);
+    for (rtc_scene* r : all) {
+        CUDA_TRY(cudaSetDevice(r->device));
+        CUDA_TRY(cudaDeviceSynchronize());
+        for (rtc_scene* o : all) {
+            if (o == r) continue;
+            cudaError_t e = cudaDeviceEnablePeerAccess(o->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+        }
+        for (int i = 0; i < 2; i++) {
+            if (r->d_cost_own[i]) cudaFree(r->d_cost_own[i]);
+            r->d_cost_own[i] = nullptr;
+            CUDA_TRY(cudaMalloc(&r->d_cost_own[i], words * sizeof(unsigned)));
+            CUDA_TRY(cudaMemset(r->d_cost_own[i], 0, words * sizeof(unsigned)));
+        }
+    }
+    for (unsigned k = 0; k < n; k++) {
+        rtc_scene* r = all[k];
+        r->share.rank = k;
+        r->share.n = n;
+        r->share.words = words;
+        r->share.external = false;
+        for (int i = 0; i < 2; i++)
+            for (unsigned j = 0; j < n; j++) r->share.cost[i][j] = all[j]->d_cost_own[i];
+        r->tile_cap = n_tiles;
+        r->pending = 0;
+        r->order_tiles = 0;
+        r->parity = 0;
+    }
+    CUDA_TRY(cudaSetDevice(s->device));
+    return RTC_OK;
+}
 
 static int launch_mega(const rtc_scene* s, const RenderParams& P, int lpp, cudaStream_t stream) {
     if (s->d.n_meshes > 0)
@@ -178,7 +249,9 @@ void rtc_scene_destroy(rtc_scene* s) {
     cudaDeviceSynchronize();  // frames may still be on a stream
     if (s->slab) cudaFree(s->slab);
     if (s->d_counters) cudaFree(s->d_counters);
-    if (s->d_tile_cost) cudaFree(s->d_tile_cost);
+    for (int i = 0; i < 2; i++)
+        if (s->d_cost_own[i]) cudaFree(s->d_cost_own[i]);
+    if (s->d_scratch) cudaFree(s->d_scratch);
     if (s->d_tile_order) cudaFree(s->d_tile_order);
     for (int i = 0; i < 2; i++) {
         if (s->wf_rays[i]) cudaFree(s->wf_rays[i]);
@@ -547,10 +620,14 @@ static int resolve_frame(rtc_scene* s, int slot) {
     f.stats.secondary_rays = c[3];
     f.stats.pixels = f.pixels;
     f.stats.kernel_ms = ms;  // render kernel + the two tile order kernels behind it
-    f.stats.launches = f.lpt ? 3 : 1;
+    f.stats.launches = f.order_made ? 3 : 1;  // render kernel (+ the two kernels of tile_order.cu when this frame made a new order)
     f.stats.kernel = f.lpp != 1 ? 2u : 0u;
     f.stats.shadow_rays_culled = c[5];
     if (s->best_ms[f.best_slot] < 0.0f || ms < s->best_ms[f.best_slot]) s->best_ms[f.best_slot] = ms;
+    static const bool trace = std::getenv("RTC_TRACE_FRAMES") != nullptr;
+    if (trace)
+        std::fprintf(stderr, "frame: dev %d px %llu candidate %d lanes/px %d ordered %d recorded %d order made %d  %.4f ms\n", s->device,
+                     (unsigned long long)f.pixels, f.best_slot, f.lpp, (int)f.ordered, (int)f.lpt, (int)f.order_made, ms);
     f.state = 2;
     f.rc = RTC_OK;
     if (c[4]) {
@@ -568,7 +645,7 @@ static int resolve_frame(rtc_scene* s, int slot) {
 // frame's statistics are ready on return (the wavefront path and the first frames of a scene, whose times pick the
 // kernel, always are).
 static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, const Target& tg,
-                         cudaStream_t stream, bool wait, int* slot_out) {
+                         cudaStream_t stream, bool wait, int* slot_out, bool dealt = false) {
     if (!s || !cam) return fail(RTC_ERR_INVALID, "render: NULL scene or camera");
     if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
     if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
@@ -606,6 +683,25 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.tiles_x = (unsigned)((cam->hsize + RTC_TILE_W - 1) / RTC_TILE_W);
     const unsigned n_tile_rows = (unsigned)((P.rows + RTC_TILE_H - 1) / RTC_TILE_H);
     P.n_items = (unsigned long long)P.tiles_x * n_tile_rows * 32ull;
+    // dealt: this renderer and share.n - 1 others render ONE whole frame between them, tile by tile (RenderParams::deal_n)
+    P.deal_n = dealt ? s->share.n : 1u;
+    P.deal_rank = dealt ? s->share.rank : 0u;
+    // runs of 8 consecutive entries of the order per renderer: a renderer's tiles stay neighbours (shared BVH nodes and
+    // texels in L1) while every cost bucket is still spread evenly (measured on one B200 rendering 1/8 shares: dealt one by
+    // one cover.json 0.73 ms, teapot 0.133 against 0.49 / 0.114 for row partitions; RTC_DEAL_SHIFT overrides)
+    static const unsigned deal_shift = [] {
+        const char* e = std::getenv("RTC_DEAL_SHIFT");
+        int v = e ? std::atoi(e) : 3;
+        return (unsigned)(v >= 0 && v <= 8 ? v : 3);
+    }();
+    P.deal_shift = dealt ? deal_shift : 0u;
+    const size_t n_tiles = (size_t)(P.n_items / 32);  // of the frame (dealt) or of the partition
+    if (dealt) {
+        if (P.n_parts != 1 || !tg.full_frame || tg.spread_rows) return fail(RTC_ERR_INVALID, "render: a shared frame is a whole frame in device memory");
+        const size_t run = size_t(1) << P.deal_shift, round = run * P.deal_n, rem = n_tiles % round, lo = (size_t)P.deal_rank * run;
+        const size_t mine = n_tiles / round * run + (rem > lo ? std::min(rem - lo, run) : 0);
+        P.n_items = (unsigned long long)mine * 32ull;
+    }
     {
         // Order of the tile rows.  Frame in device memory: top to bottom (neighbouring rows share BVH nodes and
         // texels).  Frame in mapped host memory: groups of rows in golden-ratio stride order, so that pixels are
@@ -645,9 +741,9 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     P.out = tg.rgb;
     P.out8 = tg.rgba;
     P.counters = s->d_counters;
-    const size_t n_px = (size_t)(P.rows * cam->hsize);
+    const size_t n_px = dealt ? (size_t)(P.n_items) : (size_t)(P.rows * cam->hsize);  // (dealt: pixel slots of its tiles)
     F.pixels = n_px;
-    if (P.rows == 0) {  // an empty partition: nothing to do, statistics all zero
+    if (P.rows == 0 || P.n_items == 0) {  // an empty partition: nothing to do, statistics all zero
         F.state = 2;
         s->seq_next++;
         *slot_out = slot;
@@ -656,35 +752,44 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (s->tuned_pixels != n_px) {  // another frame size (or partition): measure again
         s->tuned_pixels = n_px;
         s->frames = 0;
-        s->best_ms[0] = s->best_ms[1] = s->best_ms[2] = -1.0f;
-        s->order_tiles = 0;
+        for (float& b : s->best_ms) b = -1.0f;
     }
     int which = forced_kernel();
+    if (dealt && which == 1) which = 0;  // the wavefront path renders row partitions only
     bool measuring = false;
     if (which < 0) {
-        // first guess: the wavefront pays where rays recurse and the frame is big enough to amortise its launches
-        const int guess = (s->has_secondary && n_px >= (1u << 19)) ? 1 : 0;
+        const int guess = 0;
         const bool three = forced_lpp(s) < 0 && mixed_candidate(s, n_px);
-        if (s->frames < 4) {
-            which = (s->frames & 1) ? 1 - guess : guess;  // two frames each: the first one is cold
+        // Frames 0-2: megakernel (the first is cold, the second makes the tile order, the third is what a steady frame
+        // costs), frames 3-4: wavefront (the first loads its kernels), then -- small partitions -- two frames each with
+        // the tiles that cost >= 8x, >= 4x, >= 2x the mean four-fold.  The best time of each candidate counts.
+        (void)guess;
+        if (s->frames < 3) {
+            which = 0;
             measuring = true;
-        } else if (three && s->frames < 6) {
-            which = 2;
+        } else if (s->frames < 5 && !dealt) {
+            which = 1;
+            measuring = true;
+        } else if (three && s->frames < (dealt ? 9 : 11)) {  // (a shared frame has no wavefront frames)
+            which = 2 + (s->frames - (dealt ? 3 : 5)) / 2;
             measuring = true;
         } else {
-            which = (s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
-            if (three && s->best_ms[2] >= 0.0f && s->best_ms[2] < s->best_ms[which]) which = 2;
+            which = (!dealt && s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
+            if (three)
+                for (int k = 2; k < 5; k++)
+                    if (s->best_ms[k] >= 0.0f && s->best_ms[k] < s->best_ms[which]) which = k;
         }
     }
     int lpp = forced_lpp(s);
-    if (lpp < 0) lpp = which == 2 ? 0 : 1;
-    F.best_slot = which == 2 ? 2 : 0;  // where a megakernel frame's time is recorded
+    if (lpp < 0) lpp = which >= 2 ? 0 : 1;
+    F.best_slot = which >= 2 ? which : 0;  // where a megakernel frame's time is recorded
     s->frames++;
     if (which == 1) {
         rtc_stats local{};
         int rc = render_wavefront(s, P, stream, &local);  // synchronous: its queue counters decide about a redo
         if (rc != RTC_ERR_CAPACITY + 1000) {
             if (rc == RTC_OK && (s->best_ms[1] < 0.0f || local.kernel_ms < s->best_ms[1])) s->best_ms[1] = local.kernel_ms;
+            if (std::getenv("RTC_TRACE_FRAMES")) std::fprintf(stderr, "frame: dev %d px %llu wavefront  %.4f ms\n", s->device, (unsigned long long)n_px, local.kernel_ms);
             CUDA_TRY(cudaEventRecord(s->rev2[slot], stream));
             F.stats = local;
             F.state = 2;
@@ -695,7 +800,6 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         }
         s->best_ms[1] = 1e30f;  // queue overflow: this scene stays with the megakernel; redo the frame below
     }
-    const size_t n_tiles = (size_t)(P.n_items / 32);
     // Tiles in the order of their cost in the previous frame of this size (tile_order.cu); RTC_LPT=0 keeps the plain order.
     // Not for canvases in mapped host memory: there the time a warp spends on a tile is mostly the back-pressure of its
     // stores on the PCIe link, and the even byte rate of the strided order matters more (measured: e2e 1.49 -> 1.91 ms;
@@ -705,28 +809,72 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         const char* e = std::getenv("RTC_LPT");
         return e ? std::atoi(e) : 1;
     }();
-    const bool lpt = lpt_env == 2 || (lpt_env == 1 && !tg.spread_rows);
+    const bool lpt = dealt || lpt_env == 2 || (lpt_env == 1 && !tg.spread_rows);
     F.lpt = lpt;
-    if (lpt) {
-        if (s->tile_cap < n_tiles) {
-            CUDA_TRY(cudaStreamSynchronize(stream));  // frames of the old size may still read the arrays
-            if (s->d_tile_cost) cudaFree(s->d_tile_cost);
-            if (s->d_tile_order) cudaFree(s->d_tile_order);
-            s->d_tile_cost = s->d_tile_order = nullptr;
-            s->tile_cap = 0;
-            // costs, then the scratch counts of tile_order.cu (4 per 1024 tiles)
-            CUDA_TRY(cudaMalloc(&s->d_tile_cost, (n_tiles + 4 * (n_tiles / 1024 + 1) + 1) * sizeof(unsigned)));
-            CUDA_TRY(cudaMalloc(&s->d_tile_order, n_tiles * sizeof(unsigned)));
-            s->tile_cap = n_tiles;
-            s->order_tiles = 0;
-        }
-        CUDA_TRY(cudaMemsetAsync(s->d_tile_cost, 0, n_tiles * sizeof(unsigned), stream));
-        P.tile_cost = s->d_tile_cost;
-        P.tile_order = s->order_tiles == n_tiles ? s->d_tile_order : nullptr;
-        P.heavy_tiles = s->d_tile_cost + n_tiles + 4 * ((n_tiles + 1023) / 1024);
-    }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->rev0[slot], stream));
+    if (lpt) {
+        const size_t words = cost_words(n_tiles);
+        if (s->share.external) {
+            if (words > s->share.words) return fail(RTC_ERR_INVALID, "render: the shared tile buffers are too small for this frame");
+        } else if (s->tile_cap < n_tiles) {
+            if (s->share.n > 1) return fail(RTC_ERR_INVALID, "render: frame larger than the replicas' tile buffers");
+            CUDA_TRY(cudaStreamSynchronize(stream));  // frames of the old size may still use the arrays
+            for (int i = 0; i < 2; i++) {
+                if (s->d_cost_own[i]) cudaFree(s->d_cost_own[i]);
+                s->d_cost_own[i] = nullptr;
+                CUDA_TRY(cudaMalloc(&s->d_cost_own[i], words * sizeof(unsigned)));
+                CUDA_TRY(cudaMemsetAsync(s->d_cost_own[i], 0, words * sizeof(unsigned), stream));
+                s->share.cost[i][0] = s->d_cost_own[i];
+            }
+            s->share.words = words;
+            s->tile_cap = n_tiles;
+            s->pending = 0;
+        }
+        if (s->order_cap < n_tiles) {  // the arrays that are never shared: bucket counts, the permutation
+            CUDA_TRY(cudaStreamSynchronize(stream));
+            if (s->d_scratch) cudaFree(s->d_scratch);
+            if (s->d_tile_order) cudaFree(s->d_tile_order);
+            s->d_scratch = s->d_tile_order = nullptr;
+            s->order_cap = 0;
+            CUDA_TRY(cudaMalloc(&s->d_scratch, (4 * (n_tiles / 1024 + 1) + 3) * sizeof(unsigned)));
+            CUDA_TRY(cudaMalloc(&s->d_tile_order, n_tiles * sizeof(unsigned)));
+            s->order_cap = n_tiles;
+            s->order_tiles = 0;
+        }
+        const int b = s->parity;
+        unsigned* mine_prev = s->share.cost[b ^ 1][s->share.rank];
+        rtc_scene::View view{};
+        view.cam = *cam;
+        view.depth = max_depth;
+        view.tile_rows = P.tile_rows, view.part = P.part, view.n_parts = P.n_parts, view.deal_rank = P.deal_rank, view.deal_n = P.deal_n;
+        if (s->pending == n_tiles) {
+            // the previous frame's costs (complete in EVERY renderer's copy: a shared frame ends with a barrier) -> the order
+            CUDA_TRY((cudaError_t)launch_tile_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
+                                                    s->d_scratch, s->d_tile_order, (unsigned)n_tiles, stream));
+            s->order_tiles = n_tiles;
+            s->order_view = s->pending_view;
+            F.order_made = true;
+        }
+        if (s->pending) CUDA_TRY(cudaMemsetAsync(mine_prev, 0, s->share.words * sizeof(unsigned), stream));  // clean for its next turn
+        s->pending = 0;
+        P.tile_order = s->order_tiles == n_tiles ? s->d_tile_order : nullptr;
+        P.heavy_tiles = s->d_scratch + 4 * ((n_tiles + 1023) / 1024) + (which >= 2 ? which - 2 : 0);
+        static const bool always = [] {
+            const char* e = std::getenv("RTC_LPT_ALWAYS");
+            return e && e[0] == '1';
+        }();
+        const bool record = always || !(P.tile_order && std::memcmp(&s->order_view, &view, sizeof view) == 0);
+        F.ordered = P.tile_order != nullptr;
+        F.lpt = record;
+        if (record) {
+            for (unsigned r = 0; r < P.deal_n; r++) P.cost_peer[r] = dealt ? s->share.cost[b][r] : s->share.cost[b][s->share.rank];
+            P.cost_tiles = (unsigned)(cost_words(n_tiles) - 2);
+            s->parity ^= 1;
+            s->pending = n_tiles;
+            s->pending_view = view;
+        }
+    }
     // The mixed kernel needs the order of a previous frame.  Without one (first frame of a size; canvases in mapped host
     // memory, which keep the strided order) the candidate is two lanes per pixel everywhere: measured on the 1/8 partition
     // of dragons.json 1080p without an order, 0.49 -> 0.39 ms.
@@ -734,11 +882,6 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     F.lpp = lpp;
     P.n_items *= (unsigned long long)(lpp ? lpp : 1);
     CUDA_TRY((cudaError_t)launch_mega(s, P, lpp, stream));
-    if (lpt) {  // the next frame's order, made from this frame's costs right behind the kernel, on the same stream
-        CUDA_TRY((cudaError_t)launch_tile_order(s->d_tile_cost, s->d_counters + 6, s->d_tile_cost + n_tiles, s->d_tile_order,
-                                                (unsigned)n_tiles, stream));
-        s->order_tiles = n_tiles;
-    }
     CUDA_TRY(cudaEventRecord(s->rev1[slot], stream));
     CUDA_TRY(cudaMemcpyAsync(s->h_counters + 8 * slot, s->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream));
     CUDA_TRY(cudaEventRecord(s->rev2[slot], stream));
@@ -782,7 +925,9 @@ static int render_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, cons
     const bool whole = !part || part->n_parts <= 1;
     if (s->replicas.empty() || !whole) {
         int slot = -1;
-        int rc = enqueue_frame(s, cam, max_depth, part, tg, stream, wait, &slot);
+        // a scene whose tiles are shared with other processes (rtc_scene_share_tiles) renders ITS share of a whole frame
+        const bool dealt = whole && s->share.external && s->share.n > 1 && tg.full_frame && !tg.spread_rows;
+        int rc = enqueue_frame(s, cam, max_depth, part, tg, stream, wait, &slot, dealt);
         if (!wait || slot < 0) return rc;
         while (s->seq_next - s->seq_pop > 1) pop_frame(s, nullptr);  // frames put on the stream earlier and never fetched
         const int rp = pop_frame(s, stats);
@@ -790,20 +935,35 @@ static int render_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, cons
     }
     const unsigned n = 1u + (unsigned)s->replicas.size();
     tg.full_frame = true;
+    // Frame in device memory: the tiles are DEALT by last frame's cost (every device gets its share of the expensive
+    // ones).  Canvas in mapped host memory: interleaved 8-row tiles in strided row order (even byte rate on every link).
+    const bool dealt = !tg.spread_rows;
+    if (dealt) {
+        int rs = ensure_replica_share(s, frame_tiles(cam->hsize, cam->vsize));
+        if (rs) return rs;
+    }
     CUDA_TRY(cudaSetDevice(s->device));
     // the replicas start when the caller's stream has reached this point (its earlier work may still read the target)
     CUDA_TRY(cudaEventRecord(s->ev0, stream));
     int rc = RTC_OK;
     std::vector<int> slots(n, -1);
+    std::vector<cudaEvent_t> before(n, nullptr);  // end of the frame each device rendered last
+    for (unsigned j = 0; j < n; j++) {
+        rtc_scene* o = j == 0 ? s : s->replicas[j - 1];
+        if (o->seq_next > 0) before[j] = o->rev2[(int)((o->seq_next - 1) % rtc_scene::kRing)];
+    }
     for (unsigned k = 0; k < n && rc == RTC_OK; k++) {
         rtc_scene* r = k == 0 ? s : s->replicas[k - 1];
         rtc_partition p = {8u, k, n};
         cudaStream_t st = k == 0 ? stream : r->own_stream;
-        if (k > 0) {
-            CUDA_TRY(cudaSetDevice(r->device));
-            CUDA_TRY(cudaStreamWaitEvent(st, s->ev0, 0));
+        CUDA_TRY(cudaSetDevice(r->device));
+        if (k > 0) CUDA_TRY(cudaStreamWaitEvent(st, s->ev0, 0));
+        if (dealt) {
+            // a frame starts when the frame before it is through on EVERY device (it wrote costs into all of them)
+            for (unsigned j = 0; j < n; j++)
+                if (j != k && before[j]) CUDA_TRY(cudaStreamWaitEvent(st, before[j], 0));
         }
-        rc = enqueue_frame(r, cam, max_depth, &p, tg, st, false, &slots[k]);
+        rc = enqueue_frame(r, cam, max_depth, dealt ? nullptr : &p, tg, st, false, &slots[k], dealt);
     }
     CUDA_TRY(cudaSetDevice(s->device));
     for (unsigned k = 1; k < n; k++) {
@@ -848,6 +1008,40 @@ int rtc_render_device_async(rtc_scene* s, const rtc_camera* cam, int max_depth, 
     tg.rgb = d_frame;
     tg.full_frame = true;
     return render_frame(s, cam, max_depth, part, tg, (cudaStream_t)stream, false, nullptr);
+}
+
+uint64_t rtc_tile_share_words(uint64_t hsize, uint64_t vsize) { return cost_words(frame_tiles(hsize, vsize)); }
+
+int rtc_scene_share_tiles(rtc_scene* s, const rtc_tile_share* sh) {
+    if (!s) return fail(RTC_ERR_INVALID, "rtc_scene_share_tiles: NULL scene");
+    if (!s->replicas.empty()) return fail(RTC_ERR_INVALID, "rtc_scene_share_tiles: the scene is replicated inside this process already");
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    s->pending = 0;
+    s->order_tiles = 0;
+    s->parity = 0;
+    s->tuned_pixels = 0;
+    if (!sh || sh->n_ranks <= 1) {  // back to a renderer by itself
+        s->share = rtc_scene::Share();
+        for (int i = 0; i < 2; i++) s->share.cost[i][0] = s->d_cost_own[i];
+        s->share.words = s->tile_cap ? cost_words(s->tile_cap) : 0;
+        for (int i = 0; i < 2; i++)
+            if (s->d_cost_own[i]) CUDA_TRY(cudaMemset(s->d_cost_own[i], 0, s->share.words * sizeof(unsigned)));
+        return RTC_OK;
+    }
+    if (sh->n_ranks > RTC_MAX_SHARE || sh->rank >= sh->n_ranks) return fail(RTC_ERR_INVALID, "rtc_scene_share_tiles: bad rank / n_ranks (at most 8 renderers)");
+    for (int i = 0; i < 2; i++)
+        for (unsigned r = 0; r < sh->n_ranks; r++)
+            if (!sh->cost[i][r]) return fail(RTC_ERR_INVALID, "rtc_scene_share_tiles: NULL buffer");
+    s->share.rank = sh->rank;
+    s->share.n = sh->n_ranks;
+    s->share.words = (size_t)sh->words;
+    s->share.external = true;
+    for (int i = 0; i < 2; i++)
+        for (unsigned r = 0; r < sh->n_ranks; r++) s->share.cost[i][r] = static_cast<unsigned*>(sh->cost[i][r]);
+    // this renderer's own two buffers start clean (the caller puts a barrier behind the call: see rtc_b200.h)
+    for (int i = 0; i < 2; i++) CUDA_TRY(cudaMemset(s->share.cost[i][sh->rank], 0, s->share.words * sizeof(unsigned)));
+    return RTC_OK;
 }
 
 int rtc_stats_fetch(rtc_scene* s, rtc_stats* stats_out, uint32_t max_frames, uint32_t* n_out) {

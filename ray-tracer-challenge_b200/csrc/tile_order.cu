@@ -73,7 +73,11 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
         __syncthreads();
     }
     (void)total;
-    if (blockIdx.x == 0 && tid == 0) *heavy = s_base[1];  // block 0: all of bucket 0 (cost >= 8x the mean) lies before its bucket 1
+    if (blockIdx.x == 0 && tid == 0) {  // block 0: all of bucket b lies before its own bucket b + 1
+        heavy[0] = s_base[1];  // tiles that cost >= 8x the mean
+        heavy[1] = s_base[2];  // ... >= 4x
+        heavy[2] = s_base[3];  // ... >= 2x
+    }
     const unsigned i = blockIdx.x * T + tid;
     const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
     unsigned rank = 0;  // among the tiles of my bucket in my warp
@@ -98,7 +102,7 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
 }
 }  // namespace
 
-// scratch: 4 * ceil(n_tiles / 1024) + 1 unsigned (the last one receives the number of tiles in bucket 0); sum: the render kernel's sum of all tile costs (device memory)
+// scratch: 4 * ceil(n_tiles / 1024) + 3 unsigned (the last three receive the number of tiles that cost >= 8x, 4x, 2x the mean); sum: the render kernel's sum of all tile costs (device memory)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
                       cudaStream_t stream) {
     if (!n_tiles) return 0;

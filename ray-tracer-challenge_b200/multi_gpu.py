@@ -13,6 +13,11 @@ is the framebuffer, assembled on rank 0 in one of two ways:
                host-side logic the CPU tests exercise.
 
 Neither class renders anything itself: both only own buffers and the exchange.
+
+The scene is parsed ONCE: broadcast_scene sends rank 0's flattened blob and camera to every rank (NCCL broadcast on
+GPUs, gloo on the CPU tests) -- no rank but 0 reads a JSON, OBJ or PNG file.  With PeerFrame the ranks do not keep fixed
+row partitions either: TileShare gives every rank's scene the peer-mapped cost buffers of all ranks
+(rtc_scene_share_tiles), and the tiles of each frame are dealt by what they cost in the frame before.
 """
 import torch
 import torch.distributed as dist
@@ -72,6 +77,45 @@ class PeerFrame:
         into the frame have been issued and completed."""
         self.handle.barrier()
         return self.frame
+
+
+def broadcast_scene(blob, cam_struct, rank, device, group=None):
+    """rank 0's (blob bytes, ctypes rtc_camera) -> the same pair on every rank.  The blob travels as a uint8 tensor on
+    `device` (NCCL over NVLink on GPUs), the 168-byte camera with it."""
+    import ctypes
+    head = torch.zeros(2, dtype=torch.int64, device=device)
+    if rank == 0:
+        cam_bytes = ctypes.string_at(ctypes.byref(cam_struct), ctypes.sizeof(cam_struct))
+        head[0], head[1] = len(blob), len(cam_bytes)
+    dist.broadcast(head, src=0, group=group)
+    n_blob, n_cam = int(head[0]), int(head[1])
+    buf = torch.empty(n_blob + n_cam, dtype=torch.uint8, device=device)
+    if rank == 0:
+        buf.copy_(torch.frombuffer(bytearray(blob + cam_bytes), dtype=torch.uint8))
+    dist.broadcast(buf, src=0, group=group)
+    if rank == 0:
+        return blob, cam_struct
+    host = buf.cpu().numpy().tobytes()
+    import importlib
+    cam = importlib.import_module(__package__).rtc_camera()
+    assert n_cam == ctypes.sizeof(cam)
+    ctypes.memmove(ctypes.byref(cam), host[n_blob:], n_cam)
+    return host[:n_blob], cam
+
+
+class TileShare:
+    """Two symmetric cost buffers per rank, every rank's mapped into every rank (rtc_scene_share_tiles).  Collective."""
+
+    def __init__(self, world_obj, width, height, rank, world, device, pkg, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.words = int(pkg.lib().rtc_tile_share_words(width, height))
+        self.buf = symm_mem.empty(2 * self.words, dtype=torch.int32, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        ptrs = [[int(self.handle.buffer_ptrs[r]) + b * self.words * 4 for r in range(world)] for b in range(2)]
+        world_obj.share_tiles(rank, world, self.words, ptrs)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)  # every rank's buffers are clean before anyone renders
 
 
 class SharedHostFrame:

@@ -93,3 +93,29 @@ def test_shared_host_frame_world2_gloo(tmp_path):
     for y in range(height):
         assert torch.all(frame[y, :, 0] == y + 1)
         assert torch.all(frame[y, :, 1] == (y // tile_rows) % world)
+
+
+def _bcast_worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        pkg = importlib.import_module("ray-tracer-challenge_b200")
+        mg = importlib.import_module("ray-tracer-challenge_b200.multi_gpu")
+        from tests import scenes
+        blob = cam = None
+        if rank == 0:  # only rank 0 parses the scene
+            blob, cam = pkg.load_blob(scenes.SMOKE_SCENE, "", 96, 64)
+        blob, cam = mg.broadcast_scene(blob, cam, rank, torch.device("cpu"))
+        info = pkg.inspect_blob(blob)  # every rank can build the device scene from what it received
+        with open(os.path.join(out_dir, "r%d.txt" % rank), "w") as f:
+            import hashlib
+            f.write("%s %d %d %r %d" % (hashlib.sha256(blob).hexdigest(), cam.hsize, cam.vsize, cam.pixel_size, info.n_leaves))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_scene_broadcast_world2_gloo(tmp_path):
+    """The N > 1 path parses the scene on rank 0 only and broadcasts blob + camera (NCCL on GPUs, gloo here)."""
+    mp.spawn(_bcast_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    a, b = (open(os.path.join(str(tmp_path), "r%d.txt" % r)).read() for r in range(2))
+    assert a == b and a.split()[1:3] == ["96", "64"]

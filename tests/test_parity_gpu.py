@@ -225,7 +225,7 @@ def test_small_partitions_measure_two_lanes_per_pixel(pkg):
     if s is None:
         pytest.skip("reference assets not staged")
     info = pkg.parse_scene(s[0], s[1], 640, 360)
-    frames = [info.camera.render(info.world, partition=(8, 2, 4)).pixels.copy() for _ in range(8)]
+    frames = [info.camera.render(info.world, partition=(8, 2, 4)).pixels.copy() for _ in range(12)]
     assert frames[0].any()
     for f in frames[1:]:
         assert np.array_equal(frames[0], f)
@@ -462,3 +462,41 @@ def test_replicated_scene_uses_all_devices(pkg):
     pkg.free_pinned(pinned)
     many.close()
     one.close()
+
+
+@pytest.mark.parametrize("n", [2, 3])
+def test_frame_shared_tile_by_tile_is_the_same_frame(pkg, n):
+    """rtc_scene_share_tiles on ONE GPU: n scenes (the "ranks") take the tiles of one cost order in turn and add every
+    tile's cost to all n cost buffers.  Rendered round by round into one frame, every round gives the whole frame, bit
+    for bit, and the ray counts add up -- first round (no order yet), later rounds (cost order, mixed kernel included)."""
+    import torch
+    s = scenes.shipped_scene("dragons")
+    text, assets, (w, h) = (s[0], s[1], (500, 203)) if s else (scenes.SMOKE_SCENE, "", (163, 97))
+    blob, cam = pkg.load_blob(text, assets, w, h)
+    camera = pkg.Camera(cam)
+    ref_world = pkg.World(blob, 0)
+    want = camera.render(ref_world)
+    words = int(pkg.lib().rtc_tile_share_words(w, h))
+    bufs = [torch.zeros(2 * words, dtype=torch.int32, device="cuda") for _ in range(n)]
+    ptrs = [[bufs[r].data_ptr() + b * words * 4 for r in range(n)] for b in range(2)]
+    worlds = [pkg.World(blob, 0) for _ in range(n)]
+    for r, wld in enumerate(worlds):
+        wld.share_tiles(r, n, words, ptrs)
+    frame = torch.empty((h, w, 3), dtype=torch.float64, device="cuda")
+    for rnd in range(12):  # past the first-frames measurement: rounds 4-9 run the mixed kernel on small shares
+        frame.fill_(float("nan"))
+        rays = 0
+        for wld in worlds:
+            rays += camera.render_device_frame(wld, frame.data_ptr()).rays
+        torch.cuda.synchronize()
+        assert np.array_equal(frame.cpu().numpy(), want.pixels), "round %d" % rnd
+        assert rays == want.stats.rays
+    # every rank's copy of the costs is the same
+    torch.cuda.synchronize()
+    for r in range(1, n):
+        assert torch.equal(bufs[0], bufs[r])
+    worlds[0].share_tiles(0, 1, 0, None)  # back to a renderer by itself
+    frame.fill_(0)
+    camera.render_device_frame(worlds[0], frame.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(frame.cpu().numpy(), want.pixels)
