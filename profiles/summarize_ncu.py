@@ -42,6 +42,34 @@ def traffic_json(path, out_path, note):
         f.write("\n")
 
 
+def roofline_json(path, out_path, note):
+    """profiles/r2_roofline_inputs.json for bench.py's roofline block: what ONE launch of the profiled kernel executed
+    and moved (warp instructions, DRAM bytes) and how busy the pipes were."""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    rec = dict(zip(hdr, rows[2]))
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+    def num(k):
+        return float(rec[k].replace(",", ""))
+    dram = sum(num(k) * scale[units[hdr.index(k)]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+    with open(out_path, "w") as f:
+        json.dump({"kernel": rec.get("Kernel Name"), "source": "ncu --set full, %s, %s" % (path.split("/")[-1], note),
+                   "warp_instructions_per_launch": num("smsp__inst_executed.sum"),
+                   "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                   "fp64_pipe_pct": num("sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active"),
+                   "threads_per_inst": num("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                   "l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": num("lts__t_sector_hit_rate.pct"),
+                   "dram_bytes_per_launch": dram, "dram_pct": num("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+                   "registers_per_thread": num("launch__registers_per_thread"),
+                   "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"),
+                   "duration_under_ncu_ms": num("gpu__time_duration.sum") * {"us": 1e-3, "ms": 1.0, "ns": 1e-6, "s": 1e3}.get(
+                       units[hdr.index("gpu__time_duration.sum")], 1.0)}, f, indent=1)
+        f.write("\n")
+
+
 def main(path):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
@@ -59,7 +87,9 @@ def main(path):
 
 
 if __name__ == "__main__":
-    if len(sys.argv) > 2 and sys.argv[2] == "--traffic":
+    if len(sys.argv) > 2 and sys.argv[2] == "--roofline":
+        roofline_json(sys.argv[1], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
+    elif len(sys.argv) > 2 and sys.argv[2] == "--traffic":
         traffic_json(sys.argv[1], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "")
     else:
         main(sys.argv[1])

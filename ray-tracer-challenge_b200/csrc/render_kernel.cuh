@@ -96,9 +96,10 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 // dependent trips behind a pixel shrinks from 1 + n_lights per hit to 1 + ceil(n_lights / LPP), at the price of LPP
 // times the closest-hit work: a loss while there are enough pixels to fill the machine, a gain for the small
 // partitions of a multi-GPU frame, whose time is the chain of their most expensive tile (profiles/README.md).
-// LEAN = the scene has no CSG objects, no guard boxes (hence no stray triangles among the prims) and only solid
-// patterns (rtc_api.cu lean_scene: dragons.json, teapot.json, cover.json ...): the instantiation carries none of that
-// code -- fewer instructions to fetch (the render loop is larger than the instruction cache) and fewer live registers.
+// LEAN = the scene has no CSG objects, no guard boxes (hence no stray triangles among the prims) and only solid colours
+// or simple patterns over two solid colours (rt_pattern.cuh simple_pattern_color; rtc_api.cu decides: 10 of the 14
+// shipped scenes, dragons / teapot / cover / fresnel among them): the instantiation carries none of the other code --
+// fewer instructions to fetch (the render loop is larger than the instruction cache), no calls, fewer live registers.
 template <bool MESH, int LPP, bool LEAN>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
     static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");
@@ -355,9 +356,8 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 const rtc_material& M = S.materials[h_mat];
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
-                if constexpr (LEAN) {  // every pattern is solid (solid.zig): its colour, whatever the point
-                    const double* pc = S.patterns[M.pattern].color;
-                    pk_st(pk, PK_COLOR, v3(__ldg(pc), __ldg(pc + 1), __ldg(pc + 2)));
+                if constexpr (LEAN) {  // every pattern is a solid colour or one simple pattern over two of them
+                    pk_st(pk, PK_COLOR, simple_pattern_color(S, M.pattern, xf_point(inv, over)));
                 } else {
                     pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));
                 }

@@ -76,6 +76,36 @@ __device__ __forceinline__ V3 texel(const DScene& S, const rtc_image& im, long i
     return v3(__ldg(p), __ldg(p + 1), __ldg(p + 2));
 }
 
+// LEAN scenes (render_kernel.cuh): every material's pattern is a solid colour or ONE selecting / mixing pattern over two
+// solid colours (stripes, rings, checkers, gradient, radial gradient, blend) -- most shipped scenes.  Same operations in
+// the same order as pattern_color below performs for such a tree (weight 1: x * 1.0 and 0.0 + x are exact), without the
+// explicit stack, the texture code and the call: bit-identical, tested against the general instantiation.
+__device__ __forceinline__ V3 simple_pattern_color(const DScene& S, int root, V3 op) {
+    const rtc_pattern& P = S.patterns[root];
+    const int kind = P.kind;
+    if (kind == RTC_PAT_SOLID) return v3(__ldg(P.color), __ldg(P.color + 1), __ldg(P.color + 2));
+    M34 inv = load_m34(P.inverse);
+    V3 pp = xf_point(inv, op);
+    const double* ca = S.patterns[P.a].color;
+    const double* cb = S.patterns[P.b].color;
+    bool first;
+    if (kind == RTC_PAT_STRIPES) first = zmod(pp.x, 2.0) < 1.0;                                          // stripes.zig:27-33
+    else if (kind == RTC_PAT_RINGS) first = zmod(floor(sqrt(pp.x * pp.x + pp.z * pp.z)), 2.0) < 1.0;    // rings.zig:27-33
+    else if (kind == RTC_PAT_CHECKERS) first = zmod(floor(pp.x) + floor(pp.y) + floor(pp.z), 2.0) < 1.0;  // checkers.zig:23-29
+    else {
+        double f = 0.5;  // blend.zig:24-27
+        if (kind == RTC_PAT_GRADIENT) f = pp.x - floor(pp.x);  // gradient.zig:27-32
+        if (kind == RTC_PAT_RADIAL_GRADIENT) {                 // gradient.zig:49-55
+            double mag = sqrt(pp.x * pp.x + pp.z * pp.z);
+            f = mag - floor(mag);
+        }
+        const double wa = 1.0 - f;
+        return v3(__ldg(ca), __ldg(ca + 1), __ldg(ca + 2)) * wa + v3(__ldg(cb), __ldg(cb + 1), __ldg(cb + 2)) * f;
+    }
+    const double* c = first ? ca : cb;
+    return v3(__ldg(c), __ldg(c + 1), __ldg(c + 2));
+}
+
 struct PatTask {
     int pat;
     V3 p;      // object-space point handed to this pattern

@@ -394,8 +394,15 @@ static int create_on_device(const HostScene& hs, const std::vector<uint8_t>& sta
         // RTC_LEAN=0 keeps the general instantiation (tests compare the two)
         const char* le = std::getenv("RTC_LEAN");
         s->lean = !(le && le[0] == '0') && hs.csg_roots.empty() && hs.guards.empty();
-        for (const rtc_material& m : hs.materials)
-            if (hs.patterns[(size_t)m.pattern].kind != RTC_PAT_SOLID) s->lean = false;
+        for (const rtc_material& m : hs.materials) {  // rt_pattern.cuh simple_pattern_color covers exactly these
+            const rtc_pattern& pt = hs.patterns[(size_t)m.pattern];
+            const bool two_solids = pt.a >= 0 && pt.b >= 0 && hs.patterns[(size_t)pt.a].kind == RTC_PAT_SOLID &&
+                                    hs.patterns[(size_t)pt.b].kind == RTC_PAT_SOLID;
+            const bool simple = pt.kind == RTC_PAT_SOLID ||
+                                (two_solids && (pt.kind == RTC_PAT_STRIPES || pt.kind == RTC_PAT_RINGS || pt.kind == RTC_PAT_CHECKERS ||
+                                                pt.kind == RTC_PAT_GRADIENT || pt.kind == RTC_PAT_RADIAL_GRADIENT || pt.kind == RTC_PAT_BLEND));
+            if (!simple) s->lean = false;
+        }
     }
     if (d.n_meshes > 0) e = (cudaError_t)(s->lean ? occupancy_render_mesh_lean(&per_sm, s->smem) : occupancy_render_mesh(&per_sm, s->smem));
     else e = (cudaError_t)(s->lean ? occupancy_render_analytic_lean(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, s->smem));
