@@ -1,13 +1,7 @@
-// Instantiations of the render kernels for scenes WITHOUT triangle meshes (see render_kernel.cuh): the general one.
-#include "render_launch.cuh"
+// The wavefront kernel for scenes WITHOUT triangle meshes and the resolve kernel (render_wavefront.cuh).
 #include "render_wavefront.cuh"
 
 namespace rtc {
-
-int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream) {
-    return launch_render_impl<false, false>(S, P, lpp, grid, smem, stream);
-}
-int occupancy_render_analytic(int* blocks_per_sm, size_t smem) { return occupancy_render_impl<false, false>(blocks_per_sm, smem); }
 
 int launch_wave_analytic(const DScene& S, const WaveParams& W, int grid, size_t smem, cudaStream_t stream) {
     wave_kernel<false><<<grid, RTC_BLOCK, smem, stream>>>(S, W);

@@ -96,12 +96,17 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 // dependent trips behind a pixel shrinks from 1 + n_lights per hit to 1 + ceil(n_lights / LPP), at the price of LPP
 // times the closest-hit work: a loss while there are enough pixels to fill the machine, a gain for the small
 // partitions of a multi-GPU frame, whose time is the chain of their most expensive tile (profiles/README.md).
-// LEAN = the scene has no CSG objects, no guard boxes (hence no stray triangles among the prims) and only solid colours
-// or simple patterns over two solid colours (rt_pattern.cuh simple_pattern_color; rtc_api.cu decides: 10 of the 14
-// shipped scenes, dragons / teapot / cover / fresnel among them): the instantiation carries none of the other code --
-// fewer instructions to fetch (the render loop is larger than the instruction cache), no calls, fewer live registers.
-template <bool MESH, int LPP, bool LEAN>
+// FEAT = what of the rarer machinery the scene needs (rtc_api.cu decides per scene):
+//   RTC_FEAT_CSG       CSG objects, guard boxes, stray triangles among the prims (csg.json);
+//   RTC_FEAT_PATTERNS  patterns beyond a solid colour or ONE simple pattern over two solid colours: texture maps, perturb,
+//                      nested patterns (skybox / earth / align_check / nefertiti .json).
+// An instantiation carries only what its scene needs: fewer instructions to fetch (the render loop is larger than the
+// instruction cache: stall_no_instruction leads the ncu captures), no calls in the loop, fewer live registers.  FEAT = 0
+// ("lean") serves 9 of the 14 shipped scenes, dragons / teapot / cover / fresnel among them.
+template <bool MESH, int LPP, int FEAT>
 __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
+    constexpr bool LEAN = (FEAT & RTC_FEAT_CSG) == 0;            // no CSG / guards / stray triangles
+    constexpr bool SIMPLE_PAT = (FEAT & RTC_FEAT_PATTERNS) == 0;  // rt_pattern.cuh simple_pattern_color suffices
     static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");
     // LPP == 0 ("mixed"): four lanes per pixel on the tiles the last frame found expensive (the first *P.heavy_tiles
     // entries of tile_order: cost >= 8x the mean), one lane per pixel on all others.  The few per cent of the tiles
@@ -356,7 +361,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 const rtc_material& M = S.materials[h_mat];
                 // Material.lighting evaluates the pattern at over_point for every light (material.zig:49);
                 // it is the same colour each time, so once per hit.
-                if constexpr (LEAN) {  // every pattern is a solid colour or one simple pattern over two of them
+                if constexpr (SIMPLE_PAT) {  // every pattern is a solid colour or one simple pattern over two of them
                     pk_st(pk, PK_COLOR, simple_pattern_color(S, M.pattern, xf_point(inv, over)));
                 } else {
                     pk_st(pk, PK_COLOR, pattern_color(S, M.pattern, xf_point(inv, over), &err));

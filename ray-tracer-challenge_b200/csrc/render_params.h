@@ -19,6 +19,8 @@ namespace rtc {
 #define RTC_TILE_W (1u << RTC_TILE_W_LOG2)
 #define RTC_TILE_H (1u << RTC_TILE_H_LOG2)
 
+#define RTC_FEAT_CSG 1       // render_kernel<MESH, LPP, FEAT>: see render_kernel.cuh
+#define RTC_FEAT_PATTERNS 2
 #define RTC_MAX_SHARE 8    // renderers (GPUs) that can share one frame tile by tile (RenderParams::cost_peer)
 // Work sharing inside the mesh traversal (rt_trace.cuh trace_meshes): built, measured slower on B200, off by default.
 #ifndef RTC_STEAL
@@ -141,19 +143,16 @@ int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
                       cudaStream_t stream);
 
-// render_mesh.cu / render_analytic.cu: the two instantiations of render_kernel<MESH>.
-// smem = dynamic shared memory per CTA (the BVH traversal stacks; 0 for the analytic kernel).
-// lpp = lanes per pixel (1, 2 or 4; 0 = four on last frame's expensive tiles, one elsewhere): render_kernel<MESH, LPP>;
+// render_inst_*.cu: the instantiations of render_kernel<MESH, LPP, FEAT>, one translation unit per (MESH, FEAT).
+// smem = dynamic shared memory per CTA (parked state + the BVH traversal stacks).
+// lpp = lanes per pixel (1, 2 or 4; 0 = four on last frame's expensive tiles, one elsewhere);
 // P.n_items counts lanes, i.e. pixels x lpp (lpp 0: pixels, the kernel adds the extra lanes of the expensive tiles).
-int launch_render_mesh(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
-int launch_render_analytic(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
-int occupancy_render_mesh(int* blocks_per_sm, size_t smem);
-int occupancy_render_analytic(int* blocks_per_sm, size_t smem);
-// render_mesh_lean.cu / render_analytic_lean.cu: render_kernel<MESH, LPP, LEAN = true> for scenes without CSG objects,
-// guard boxes and non-solid patterns
-int launch_render_mesh_lean(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
-int launch_render_analytic_lean(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
-int occupancy_render_mesh_lean(int* blocks_per_sm, size_t smem);
-int occupancy_render_analytic_lean(int* blocks_per_sm, size_t smem);
+int launch_render(bool mesh, int feat, const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream);
+int occupancy_render(bool mesh, int feat, int* blocks_per_sm, size_t smem);
+#define RTC_DECLARE_INST(M, F)                                                                                          \
+    int launch_render_##M##_##F(const DScene& S, const RenderParams& P, int lpp, int grid, size_t smem, cudaStream_t stream); \
+    int occupancy_render_##M##_##F(int* blocks_per_sm, size_t smem);
+RTC_DECLARE_INST(0, 0) RTC_DECLARE_INST(0, 2) RTC_DECLARE_INST(0, 3)
+RTC_DECLARE_INST(1, 0) RTC_DECLARE_INST(1, 2) RTC_DECLARE_INST(1, 3)
 
 }  // namespace rtc

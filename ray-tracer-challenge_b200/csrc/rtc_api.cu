@@ -75,7 +75,7 @@ struct rtc_scene {
     long long* wf_acc = nullptr;
     unsigned long long* wf_counters = nullptr;
     bool has_secondary = false;  // some material is reflective or transparent: rays beyond level 0 can exist
-    bool lean = false;           // no CSG, no guard boxes, solid patterns only: render_kernel<MESH, LPP, LEAN = true>
+    int feat = 3;                // RTC_FEAT_* the scene needs: render_kernel<MESH, LPP, FEAT>
     // Which of the two kernels renders this scene faster is MEASURED (the answer depends on the scene: the
     // wavefront wins where pixels have long or branching ray trees, the megakernel where they do not and on
     // small frames): frames 1-4 alternate between the heuristic choice and the other kernel, later frames use the faster one.
@@ -163,10 +163,7 @@ static int ensure_replica_share(rtc_scene* s, size_t n_tiles) {
 }
 
 static int launch_mega(const rtc_scene* s, const RenderParams& P, int lpp, cudaStream_t stream) {
-    if (s->d.n_meshes > 0)
-        return s->lean ? launch_render_mesh_lean(s->d, P, lpp, s->grid, s->smem, stream) : launch_render_mesh(s->d, P, lpp, s->grid, s->smem, stream);
-    return s->lean ? launch_render_analytic_lean(s->d, P, lpp, s->grid, s->smem, stream)
-                   : launch_render_analytic(s->d, P, lpp, s->grid, s->smem, stream);
+    return launch_render(s->d.n_meshes > 0, s->feat, s->d, P, lpp, s->grid, s->smem, stream);
 }
 
 // RTC_KERNEL=mega|wave pins the kernel; default (auto) measures both on the first four frames of a scene.
@@ -391,9 +388,10 @@ static int create_on_device(const HostScene& hs, const std::vector<uint8_t>& sta
     s->smem = (size_t)RTC_PARK_SLOTS * RTC_BLOCK_THREADS * sizeof(double) +
               (size_t)d.stack_cap * RTC_BLOCK_THREADS * sizeof(int);
     {
-        // RTC_LEAN=0 keeps the general instantiation (tests compare the two)
+        // which of the rarer machinery the scene needs; RTC_LEAN=0 keeps the general instantiation (tests compare them)
         const char* le = std::getenv("RTC_LEAN");
-        s->lean = !(le && le[0] == '0') && hs.csg_roots.empty() && hs.guards.empty();
+        s->feat = 0;
+        if (!hs.csg_roots.empty() || !hs.guards.empty()) s->feat |= RTC_FEAT_CSG;
         for (const rtc_material& m : hs.materials) {  // rt_pattern.cuh simple_pattern_color covers exactly these
             const rtc_pattern& pt = hs.patterns[(size_t)m.pattern];
             const bool two_solids = pt.a >= 0 && pt.b >= 0 && hs.patterns[(size_t)pt.a].kind == RTC_PAT_SOLID &&
@@ -401,11 +399,13 @@ static int create_on_device(const HostScene& hs, const std::vector<uint8_t>& sta
             const bool simple = pt.kind == RTC_PAT_SOLID ||
                                 (two_solids && (pt.kind == RTC_PAT_STRIPES || pt.kind == RTC_PAT_RINGS || pt.kind == RTC_PAT_CHECKERS ||
                                                 pt.kind == RTC_PAT_GRADIENT || pt.kind == RTC_PAT_RADIAL_GRADIENT || pt.kind == RTC_PAT_BLEND));
-            if (!simple) s->lean = false;
+            if (!simple) s->feat |= RTC_FEAT_PATTERNS;
         }
+        // (CSG with simple patterns only -- csg.json -- measured no faster than the general instantiation: 1.43 against
+        // 1.38 ms at 3840x2160; that combination is not built)
+        if ((s->feat & RTC_FEAT_CSG) || (le && le[0] == '0')) s->feat = RTC_FEAT_CSG | RTC_FEAT_PATTERNS;
     }
-    if (d.n_meshes > 0) e = (cudaError_t)(s->lean ? occupancy_render_mesh_lean(&per_sm, s->smem) : occupancy_render_mesh(&per_sm, s->smem));
-    else e = (cudaError_t)(s->lean ? occupancy_render_analytic_lean(&per_sm, s->smem) : occupancy_render_analytic(&per_sm, s->smem));
+    e = (cudaError_t)occupancy_render(d.n_meshes > 0, s->feat, &per_sm, s->smem);
     if (e != cudaSuccess) return bail(e, "occupancy query");
     if (per_sm < 1) per_sm = 1;
     s->grid = prop.multiProcessorCount * per_sm;

@@ -425,10 +425,13 @@ def test_async_frames_and_stats_fetch(pkg):
     wld.close()
 
 
-@pytest.mark.parametrize("name", ["dragons", "teapot", "cover", "fresnel", "xyz", "cubes", "reflection_and_refraction", "mesh"])
+@pytest.mark.parametrize("name", ["dragons", "teapot", "cover", "fresnel", "xyz", "cubes", "reflection_and_refraction", "csg",
+                                  "skybox", "nefertiti", "mesh"])
 def test_lean_and_general_kernels_are_bit_identical(pkg, tmp_path, name):
-    """render_kernel<MESH, LPP, LEAN>: scenes without CSG, guard boxes and non-solid patterns run an instantiation that
-    carries none of that code; RTC_LEAN=0 keeps the general one.  Same frame, same ray counts, bit for bit."""
+    """render_kernel<MESH, LPP, FEAT>: a scene runs the instantiation that carries only the machinery it needs (no CSG /
+    guard code without CSG objects; the inline simple_pattern_color instead of the general pattern evaluator where
+    every pattern is a solid colour or one simple pattern over two); RTC_LEAN=0 keeps the general one (FEAT = 3).
+    Same frame, same ray counts, bit for bit."""
     if name == "mesh":
         scenes.write_mesh_obj(str(tmp_path / "torus.obj"), smooth=True, groups=False)
         text, assets, (w, h) = scenes.mesh_scene("torus.obj"), str(tmp_path), (200, 120)
