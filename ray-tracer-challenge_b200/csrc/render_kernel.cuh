@@ -27,7 +27,7 @@ struct RayTask {
 };
 #define RTC_RAY_STACK 8
 
-enum { ST_IDLE = 0, ST_CLOSEST = 1, ST_CONTAINERS = 2, ST_SHADOW = 3 };
+enum { ST_IDLE = 0, ST_CLOSEST = 1, ST_CONTAINERS = 2, ST_SHADOW = 3, ST_WAIT = 4 };  // ST_WAIT: a lane of a pipelined pixel between two jobs
 
 // color.zig:61-71 : round half away from zero, clamped to [0,255]
 __device__ __forceinline__ unsigned char quantise(double c) {
@@ -113,14 +113,22 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     // whose chains of dependent trips set the time of a small partition get the short chain; the rest of the frame
     // is not traced twice.
     constexpr bool MIXED = LPP == 0;
+    // Lanes per pixel of a heavy tile (mixed kernel).  4: as LPP = 4, all four lanes trace a hit's closest-hit query and
+    // split its lights.  8 (PIPE): the pixel's lanes work as a PIPELINE -- lane 0 only walks the chain of closest-hit
+    // queries (hit -> children -> next ray -> hit ...), and every hit it finds is handed, through the parked state in
+    // shared memory, to lanes 1 .. n_lights, which trace its shadow rays in the NEXT trip while lane 0 is already on the
+    // next ray.  A level of the ray tree then costs one trip instead of two (1 + n_lights / lanes): the chain behind the
+    // deepest pixels of a small partition -- glass boxes, 6 levels -- is what its frame time is made of.
+    constexpr int HL = RTC_HEAVY_LANES;
+    constexpr bool PIPE = MIXED && HL == 8;
     // (of the heavy tiles at the head of the order this renderer is dealt its runs, like of all others)
     unsigned long long heavy_items = 0ull;
     if (MIXED && P.tile_order) {
         const unsigned h = __ldg(P.heavy_tiles), run = 1u << P.deal_shift, round = run * P.deal_n;
         const unsigned rem = h % round, lo = P.deal_rank * run;
-        heavy_items = (unsigned long long)(h / round * run + (rem > lo ? min(rem - lo, run) : 0u)) * 128ull;
+        heavy_items = (unsigned long long)(h / round * run + (rem > lo ? min(rem - lo, run) : 0u)) * (32ull * HL);
     }
-    const unsigned long long n_items = P.n_items + heavy_items / 4 * 3;  // a heavy tile is 128 lane items instead of 32
+    const unsigned long long n_items = P.n_items + heavy_items / HL * (HL - 1);  // a heavy tile is 32 x HL lane items instead of 32
     int lpp = MIXED ? 1 : LPP;  // lanes per pixel of the tile this warp is working on
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
     double* pk = s_mem + threadIdx.x;
@@ -160,7 +168,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 long long a0 = __double_as_longlong(PK(PK_PCOL)), a1 = __double_as_longlong(PK(PK_PCOL + 1)),
                           a2 = __double_as_longlong(PK(PK_PCOL + 2));
 #pragma unroll
-                for (int sft = 1; sft < (MIXED ? 4 : LPP); sft <<= 1) {
+                for (int sft = 1; sft < (MIXED ? HL : LPP); sft <<= 1) {
                     a0 += __shfl_xor_sync(0xffffffffu, a0, sft);
                     a1 += __shfl_xor_sync(0xffffffffu, a1, sft);
                     a2 += __shfl_xor_sync(0xffffffffu, a2, sft);
@@ -213,9 +221,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                     unsigned long long pitem;  // the lanes of a pixel hold consecutive items
                     if constexpr (MIXED) {
                         const bool heavy = item < heavy_items;  // the same for the whole warp: heavy_items % 32 == 0
-                        lpp = heavy ? 4 : 1;
-                        sub = heavy ? (unsigned)item & 3u : 0u;
-                        pitem = heavy ? item >> 2 : item - heavy_items / 4 * 3;
+                        lpp = heavy ? HL : 1;
+                        sub = heavy ? (unsigned)item & (unsigned)(HL - 1) : 0u;
+                        pitem = heavy ? item / (unsigned)HL : item - heavy_items / HL * (HL - 1);
                     } else {
                         pitem = item / (unsigned)LPP;
                     }
@@ -254,6 +262,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         pk_st(pk, PK_PCOL, v3(0, 0, 0));  // +0.0 is also the bit pattern of int64 0
                         rsp = 0;
                         state = ST_CLOSEST;
+                        if (PIPE && sub != 0) state = ST_WAIT;  // (lpp == HL: only there sub != 0) a shadow lane: waits for lane 0's hits
                         if (sub == 0) n_primary++;
                     }
                     // items outside the frame are simply dropped: the lane asks again next trip
@@ -266,7 +275,10 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
         MeshTrav trav;
         bool busy = false, skip = false;
         (void)trav;
-        if (state != ST_IDLE) {
+        const bool live = state != ST_IDLE && !(PIPE && state == ST_WAIT);
+        bool publish = false;  // PIPE, lane 0 of a pixel: found a hit in this trip
+        (void)publish;
+        if (live) {
             q.o = pk_ld(pk, PK_RO);
             q.d = pk_ld(pk, PK_RD);
             if (state == ST_CLOSEST) {
@@ -311,11 +323,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
 #ifdef RTC_TRIP_PROBE
         const long long probe_t0 = clock64();
 #endif
-        busy = trace_begin<MESH, LEAN>(q, S, trav, &err, state != ST_IDLE && !skip);
+        busy = trace_begin<MESH, LEAN>(q, S, trav, &err, live && !skip);
         // every mesh through ONE warp-wide traversal loop; the full-mask votes are the points where
         // the warp reconverges, so inner-node steps and triangle tests each run with all traversing lanes
         // (and lanes that are through help those that are not: trace_meshes)
-        if constexpr (MESH) trace_meshes(q, S, trav, stack, s_mem + PK_MB * RTC_BLOCK + (threadIdx.x & ~31u), &err, busy, state != ST_IDLE, lane);
+        if constexpr (MESH) trace_meshes(q, S, trav, stack, s_mem + PK_MB * RTC_BLOCK + (threadIdx.x & ~31u), &err, busy, live, lane);
 
 #ifdef RTC_TRIP_PROBE
         {   // how long does one warp trip through the world take? [6] max cycles, [7] trips | long trips << 32
@@ -375,6 +387,10 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 // n1 = n2 = 1.0 whatever the containers list holds (world.zig:236-254): the walk is skipped.
                 if (M.transparency != 0.0 && !S.ri_all_one) state = ST_CONTAINERS;
                 else state = S.n_lights > (int)sub ? ST_SHADOW : -1;  // no lights (left for this lane): straight to the children below
+                if (PIPE && lpp == HL) {  // lane 0 of a pipelined pixel: its shadow rays are the other lanes' business
+                    publish = S.n_lights > 0;
+                    if (state == ST_SHADOW) state = -1;
+                }
             }
         } else if (state == ST_CONTAINERS) {
             double ri_hit = S.materials[S.leaves[hit_leaf].material].refractive_index;
@@ -388,6 +404,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_N2) = ri_hit;
             }
             state = S.n_lights > (int)sub ? ST_SHADOW : -1;
+            if (PIPE && lpp == HL) state = -1;
         } else if (state == ST_SHADOW) {
             // Material.lighting (material.zig:40-74)
             const rtc_light& Lg = S.lights[h_light];
@@ -430,6 +447,39 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
             }
             h_light += lpp;
             if (h_light >= S.n_lights) state = -1;
+            if (PIPE && lpp == HL) state = ST_WAIT;  // a shadow lane: one light per hit, then the next hit
+        }
+
+        if constexpr (PIPE) {
+            if (lpp == HL) {  // (the same for the whole warp)
+                // lane 0 of every pixel hands the hit it found in this trip to the pixel's shadow lanes: they copy what
+                // lighting() needs out of its parked state (ray, t, normal, colour, weight) before it moves on
+                const int src = (int)(lane & ~(unsigned)(HL - 1));
+                const bool pub = __shfl_sync(0xffffffffu, (int)publish, src) != 0;
+                const int pmat = __shfl_sync(0xffffffffu, h_mat, src);
+                const bool pdone = __shfl_sync(0xffffffffu, (int)(state == ST_IDLE), src) != 0;  // its pixel has no rays left
+                __syncwarp();
+                if (sub != 0) {
+                    if (pub && (int)sub <= S.n_lights) {
+                        const double* ppk = pk - sub;
+#pragma unroll
+                        for (int k = 0; k < 3; k++) {
+                            PK(PK_RO + k) = ppk[(PK_RO + k) * RTC_BLOCK];
+                            PK(PK_RD + k) = ppk[(PK_RD + k) * RTC_BLOCK];
+                            PK(PK_NORMAL + k) = ppk[(PK_NORMAL + k) * RTC_BLOCK];
+                            PK(PK_COLOR + k) = ppk[(PK_COLOR + k) * RTC_BLOCK];
+                        }
+                        PK(PK_T) = ppk[PK_T * RTC_BLOCK];
+                        PK(PK_RW) = ppk[PK_RW * RTC_BLOCK];
+                        h_mat = pmat;
+                        h_light = (int)sub - 1;
+                        state = ST_SHADOW;
+                    } else if (state == ST_WAIT && pdone) {
+                        state = ST_IDLE;
+                    }
+                }
+                __syncwarp();  // before lane 0 overwrites its slots with the next ray
+            }
         }
 
         if (state == -1) {

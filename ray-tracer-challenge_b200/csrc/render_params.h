@@ -19,6 +19,14 @@ namespace rtc {
 #define RTC_TILE_W (1u << RTC_TILE_W_LOG2)
 #define RTC_TILE_H (1u << RTC_TILE_H_LOG2)
 
+// lanes per pixel on the heavy tiles of the mixed kernel (render_kernel.cuh): 4, or 8 = pipelined (lane 0 the chain of
+// closest hits, lanes 1 .. n_lights the shadow rays of the hit before).  MEASURED on B200, dragons.json 1080p, one GPU
+// rendering a dealt 1/8 share (profiles/README.md): 8 lanes pipelined 0.272 ms against 0.242 with 4 (1/4 share: 0.38 / 0.30):
+// the chain of the heaviest tile does get shorter (197 -> 150 us of warp time), but a trip now lasts as long as the
+// slower of a closest-hit and a shadow traversal and the tile holds twice the warps.  4 stays.
+#ifndef RTC_HEAVY_LANES
+#define RTC_HEAVY_LANES 4
+#endif
 #define RTC_FEAT_CSG 1       // render_kernel<MESH, LPP, FEAT>: see render_kernel.cuh
 #define RTC_FEAT_PATTERNS 2
 #define RTC_MAX_SHARE 8    // renderers (GPUs) that can share one frame tile by tile (RenderParams::cost_peer)

@@ -181,7 +181,7 @@ static int forced_lpp(const rtc_scene* s) {
     if (!e) return -1;
     int lpp = std::atoi(e);
     if (lpp != 0 && lpp != 1 && lpp != 2 && lpp != 4) return -1;
-    if (lpp == 0) return s->d.n_lights >= 2 ? 0 : 1;  // mixed: four lanes per pixel on last frame's expensive tiles
+    if (lpp == 0) return s->d.n_lights >= 2 && s->d.n_lights <= RTC_HEAVY_LANES - (RTC_HEAVY_LANES == 8 ? 1 : 0) ? 0 : 1;  // mixed: several lanes per pixel on last frame's expensive tiles
     while (lpp > 1 && s->d.n_lights < lpp) lpp >>= 1;  // lanes without a light would only repeat the closest-hit query
     return lpp;
 }
@@ -194,7 +194,7 @@ static int forced_lpp(const rtc_scene* s) {
 // (profiles/README.md).
 static bool mixed_candidate(const rtc_scene* s, size_t n_px) {
     const size_t warps = (size_t)s->grid * (RTC_BLOCK_THREADS / 32);
-    return s->d.n_lights >= 2 && n_px / 32 < 8 * warps;
+    return s->d.n_lights >= 2 && s->d.n_lights <= RTC_HEAVY_LANES - (RTC_HEAVY_LANES == 8 ? 1 : 0) && n_px / 32 < 8 * warps;
 }
 
 extern "C" {
