@@ -67,6 +67,56 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 }
 #define PK(k) pk[(k) * RTC_BLOCK]
 
+// The copy warps of a frame that goes to mapped host memory (RenderParams::copy_out): take the finished tiles in the
+// order they are announced and move each to the host canvas.  A tile is 4 rows of 8 pixels x 3 doubles = 4 x 192
+// contiguous bytes: lane l moves doubles l, l + 32, l + 64 of the tile's 96, so every store instruction covers whole rows.
+// A warp claims RTC_COPY_BATCH tiles at a time -- lanes 0 .. BATCH-1 each wait for one announcement, then the loads of all
+// of them are in flight together: one tile at a time a warp is a chain of L2 round trips (claim, poll, load: ~2.5 us per
+// 768 bytes, measured: 64 copy warps moved 19 GB/s).
+#ifndef RTC_COPY_BATCH
+#define RTC_COPY_BATCH 8
+#endif
+__device__ __forceinline__ void copy_finished_tiles(const RenderParams& P) {
+    const unsigned lane = threadIdx.x & 31u;
+    for (;;) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(P.copy_ctl + 1, (unsigned)RTC_COPY_BATCH) + 1u;  // (the counters start at 0xffffffff: one memset sets up list and counters)
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= P.copy_tiles) return;
+        unsigned mine = 0xffffffffu;
+        if (lane < RTC_COPY_BATCH && base + lane < P.copy_tiles) {
+            volatile unsigned* slot = P.done_list + base + lane;
+            unsigned spins = 0;
+            while ((mine = *slot) == 0xffffffffu && ++spins < (1u << 22)) __nanosleep(200);  // (~1 s: a frame takes milliseconds)
+            if (mine == 0xffffffffu) atomicOr(P.counters + 4, (unsigned long long)ERR_COPY);  // never announced: flag the frame, do not hang
+            __threadfence();  // the tile's pixels were written before it was announced
+        }
+        __syncwarp();
+        double v[RTC_COPY_BATCH][3];
+        unsigned long long at[RTC_COPY_BATCH][3];
+#pragma unroll
+        for (int j = 0; j < RTC_COPY_BATCH; j++) {
+            const unsigned tile = __shfl_sync(0xffffffffu, mine, j);
+            const unsigned long long px0 = (unsigned long long)(tile % P.tiles_x) * RTC_TILE_W, y0 = (unsigned long long)(tile / P.tiles_x) * RTC_TILE_H;
+#pragma unroll
+            for (unsigned k = 0; k < 3; k++) {
+                const unsigned e = lane + 32u * k, row = e / (3u * RTC_TILE_W), col = e % (3u * RTC_TILE_W);  // double `col` of tile row `row`
+                const unsigned long long y = y0 + row, px = px0 + col / 3u;
+                at[j][k] = ~0ull;
+                if (tile != 0xffffffffu && y < P.cam.vsize && px < P.cam.hsize) {
+                    at[j][k] = (y * P.cam.hsize + px0) * 3ull + col;
+                    v[j][k] = __ldcg(P.out + at[j][k]);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RTC_COPY_BATCH; j++)
+#pragma unroll
+            for (unsigned k = 0; k < 3; k++)
+                if (at[j][k] != ~0ull) P.copy_out[at[j][k]] = v[j][k];
+    }
+}
+
 // MESH: the scene has triangle meshes (BVH traversal compiled in; the traversal stacks follow the
 // parked state in dynamic shared memory).  Scenes without meshes run the instantiation without it.
 // Resident CTAs per SM the register allocation aims for, measured on B200 (the kernel is latency-bound:
@@ -113,6 +163,12 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     // whose chains of dependent trips set the time of a small partition get the short chain; the rest of the frame
     // is not traced twice.
     constexpr bool MIXED = LPP == 0;
+    if constexpr (LPP == 1) {  // (a decoupled host canvas is a whole frame with one lane per pixel)
+        if (P.copy_out && blockIdx.x < P.copy_ctas) {
+            copy_finished_tiles(P);
+            return;
+        }
+    }
     // Lanes per pixel of a heavy tile (mixed kernel).  4: as LPP = 4, all four lanes trace a hit's closest-hit query and
     // split its lights.  8 (PIPE): the pixel's lanes work as a PIPELINE -- lane 0 only walks the chain of closest-hit
     // queries (hit -> children -> next ray -> hit ...), and every hit it finds is handed, through the parked state in
@@ -197,14 +253,21 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
         if (need) {
             // cost of the tile this warp is through with (clock ticks / 64), for the order of the NEXT frame
             // (added to the cost arrays of all renderers sharing the frame, so that all copies stay equal)
-            if (P.cost_peer[0] && lane == 0 && PK(PK_SPARE) >= 0.0) {
-                const long long t0 = __double_as_longlong(PK(PK_SPARE + 1));
-                const unsigned cost = (unsigned)((clock64() - t0) >> 6);
+            if (LPP == 1 && P.copy_out) __syncwarp();  // every lane's pixel stores before lane 0 announces the tile
+            if ((P.cost_peer[0] || (LPP == 1 && P.copy_out)) && lane == 0 && PK(PK_SPARE) >= 0.0) {
                 const unsigned done_tile = (unsigned)PK(PK_SPARE);
-                for (unsigned r = 0; r < P.deal_n; r++) {
-                    unsigned* cp = P.cost_peer[r];
-                    atomicAdd(cp + done_tile, cost);
-                    atomicAdd(reinterpret_cast<unsigned long long*>(cp + P.cost_tiles), (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
+                if (P.cost_peer[0]) {
+                    const long long t0 = __double_as_longlong(PK(PK_SPARE + 1));
+                    const unsigned cost = (unsigned)((clock64() - t0) >> 6);
+                    for (unsigned r = 0; r < P.deal_n; r++) {
+                        unsigned* cp = P.cost_peer[r];
+                        atomicAdd(cp + done_tile, cost);
+                        atomicAdd(reinterpret_cast<unsigned long long*>(cp + P.cost_tiles), (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
+                    }
+                }
+                if (LPP == 1 && P.copy_out) {  // for the copy warps (copy_finished_tiles): where the tile lies in the frame
+                    __threadfence();
+                    P.done_list[atomicAdd(P.copy_ctl, 1u) + 1u] = (unsigned)PK(PK_SPARE + 2);
                 }
                 PK(PK_SPARE) = -1.0;
             }
@@ -231,7 +294,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                                               ((unsigned)(pitem >> 5) & ((1u << P.deal_shift) - 1u));  // the entry of the order this renderer is dealt
                     unsigned in = (unsigned)(pitem & 31u);
                     if (P.tile_order) tile = __ldg(P.tile_order + tile);  // most expensive tiles of the last frame first
-                    if (P.cost_peer[0] && lane == 0) {
+                    if ((P.cost_peer[0] || (LPP == 1 && P.copy_out)) && lane == 0) {
                         PK(PK_SPARE) = (double)tile;
                         PK(PK_SPARE + 1) = __longlong_as_double(clock64());
                     }
@@ -242,6 +305,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         if (g < P.n_row_groups)
                             trow = (unsigned)(((unsigned long long)g * P.row_stride) % P.n_row_groups) * P.row_group + t % P.row_group;
                     }
+                    if (LPP == 1 && P.copy_out && lane == 0) PK(PK_SPARE + 2) = (double)(unsigned)(trow * P.tiles_x + tile % P.tiles_x);
                     unsigned long long pr = trow * RTC_TILE_H + (in >> RTC_TILE_W_LOG2);
                     if (px < P.cam.hsize && pr < P.rows) {
                         unsigned long long y = ((pr / P.tile_rows) * P.n_parts + P.part) * P.tile_rows + pr % P.tile_rows;

@@ -79,6 +79,14 @@ struct RenderParams {
     unsigned int cost_tiles;
     unsigned int deal_n, deal_rank;
     unsigned int deal_shift;  // the order is dealt in runs of 1 << deal_shift consecutive entries (neighbouring tiles stay with one renderer)
+    // Frame for a canvas in mapped HOST memory, decoupled from the link: the render warps store their pixels into `out`
+    // in device memory and announce every finished tile in done_list[]; the warps of the first copy_ctas CTAs do nothing
+    // but wait for announcements and move finished tiles to copy_out over PCIe in full 192-byte rows.  The link is busy
+    // from the first finished tile on and no render warp ever waits for it (render_kernel.cuh copy_finished_tiles).
+    double* copy_out;          // NULL: off
+    unsigned int* done_list;   // [copy_tiles] tiles in the order they were finished (0xffffffff: not yet)
+    unsigned int* copy_ctl;    // [0] tiles announced, [1] tiles taken by copy warps
+    unsigned int copy_ctas, copy_tiles;
     const unsigned int* heavy_tiles;  // device word: how many leading entries of tile_order cost >= 8x the mean (LPP == 0)
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };
@@ -149,7 +157,7 @@ int occupancy_wave_analytic(int* blocks_per_sm, size_t smem);
 int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 // tile_order.cu: order[] = the tiles 0..n_tiles-1, stably sorted into four cost buckets (most expensive first)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
-                      cudaStream_t stream);
+                      int last_bucket, cudaStream_t stream);
 
 // render_inst_*.cu: the instantiations of render_kernel<MESH, LPP, FEAT>, one translation unit per (MESH, FEAT).
 // smem = dynamic shared memory per CTA (parked state + the BVH traversal stacks).

@@ -20,7 +20,7 @@ namespace rtc {
 #define RTC_CSG_SEG 16
 
 enum { Q_CLOSEST = 0, Q_SHADOW = 1, Q_CONTAINERS = 2 };
-enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8, ERR_QUEUE = 16, ERR_ACC_RANGE = 32 };
+enum { ERR_TEXEL = 1, ERR_PAT_STACK = 2, ERR_CSG_CAP = 4, ERR_BVH_STACK = 8, ERR_QUEUE = 16, ERR_ACC_RANGE = 32, ERR_COPY = 64 };
 
 // One world query.  The three modes never coexist, so they share their fields:
 //                 t                 leaf        a       b            c_leaf      flag

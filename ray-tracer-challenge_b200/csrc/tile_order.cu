@@ -26,20 +26,24 @@ namespace rtc {
 namespace {
 constexpr int T = 1024;
 
-__device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum) {
-    if (sum == 0) return 3;  // nothing measured (every tile below one tick): keep the plain order
+// last: buckets beyond it are merged into it (last = 3: all four; last = 1: the tiles that cost >= 8x the mean, then ALL
+// others in their plain order -- frames whose finished tiles are streamed to a host canvas want the bulk of the tiles
+// in memory order, rtc_api.cu)
+__device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum, int last) {
+    if (sum == 0) return last;  // nothing measured (every tile below one tick): keep the plain order
     const unsigned long long c = (unsigned long long)cost * n;  // cost / mean = c / sum; cost < 2^32, n < 2^24
-    return c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+    const int b = c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+    return b < last ? b : last;
 }
 
 // counts[b * gridDim.x + block] = tiles of bucket b among the block's 1024
 __global__ void __launch_bounds__(T) tile_count_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
-                                                       unsigned* __restrict__ counts, unsigned n) {
+                                                       unsigned* __restrict__ counts, unsigned n, int last) {
     __shared__ unsigned s_cnt[4];
     if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
     __syncthreads();
     const unsigned i = blockIdx.x * T + threadIdx.x;
-    const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last) : -1;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const unsigned m = __ballot_sync(0xffffffffu, b == k);
@@ -51,35 +55,43 @@ __global__ void __launch_bounds__(T) tile_count_kernel(const unsigned* __restric
 
 __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
                                                          const unsigned* __restrict__ counts, unsigned* __restrict__ order,
-                                                         unsigned* __restrict__ heavy, unsigned n) {
+                                                         unsigned* __restrict__ heavy, unsigned n, int last) {
     __shared__ unsigned s_base[4];           // where this block's tiles of bucket b start
+    __shared__ unsigned s_start[5];          // where bucket b starts (s_start[4] = n)
     __shared__ unsigned s_warp[4][T / 32];   // tiles of bucket b in each warp, then their exclusive prefix
-    __shared__ unsigned s_red[T / 32];
+    __shared__ unsigned s_red[2][T / 32];
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     // flattened (bucket, block) index of this block's bucket b is b * gridDim.x + blockIdx.x: sum everything before it
-    const unsigned total = 4 * gridDim.x;
     for (int b = 0; b < 4; b++) {
-        const unsigned end = b * gridDim.x + blockIdx.x;
-        unsigned part = 0;
-        for (unsigned j = tid; j < end; j += T) part += counts[j];
-        for (int s = 16; s > 0; s >>= 1) part += __shfl_down_sync(0xffffffffu, part, s);
-        if (lane == 0) s_red[warp] = part;
+        const unsigned first = b * gridDim.x, end = first + blockIdx.x;
+        unsigned before = 0, mine = 0;  // tiles of the buckets before b (all blocks); tiles of bucket b in the blocks before this one
+        for (unsigned j = tid; j < end; j += T) {
+            const unsigned c = counts[j];
+            if (j < first) before += c;
+            else mine += c;
+        }
+        for (int s = 16; s > 0; s >>= 1) {
+            before += __shfl_down_sync(0xffffffffu, before, s);
+            mine += __shfl_down_sync(0xffffffffu, mine, s);
+        }
+        if (lane == 0) s_red[0][warp] = before, s_red[1][warp] = mine;
         __syncthreads();
         if (tid == 0) {
-            unsigned t = 0;
-            for (int w = 0; w < T / 32; w++) t += s_red[w];
-            s_base[b] = t;
+            unsigned t0 = 0, t1 = 0;
+            for (int w = 0; w < T / 32; w++) t0 += s_red[0][w], t1 += s_red[1][w];
+            s_start[b] = t0;
+            s_base[b] = t0 + t1;
         }
         __syncthreads();
     }
-    (void)total;
-    if (blockIdx.x == 0 && tid == 0) {  // block 0: all of bucket b lies before its own bucket b + 1
-        heavy[0] = s_base[1];  // tiles that cost >= 8x the mean
-        heavy[1] = s_base[2];  // ... >= 4x
-        heavy[2] = s_base[3];  // ... >= 2x
+    if (tid == 0) s_start[4] = n;
+    if (blockIdx.x == 0 && tid == 0) {
+        heavy[0] = s_start[1];  // tiles that cost >= 8x the mean
+        heavy[1] = s_start[2];  // ... >= 4x
+        heavy[2] = s_start[3];  // ... >= 2x
     }
     const unsigned i = blockIdx.x * T + tid;
-    const int b = i < n ? bucket_of(cost[i], n, *sum_p) : -1;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last) : -1;
     unsigned rank = 0;  // among the tiles of my bucket in my warp
 #pragma unroll
     for (int k = 0; k < 4; k++) {
@@ -98,17 +110,19 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
         s_warp[warp][lane] = incl - c;
     }
     __syncthreads();
-    if (b >= 0) order[s_base[b] + s_warp[b][warp] + rank] = i;
+    if (b < 0) return;
+    const unsigned pos = s_base[b] + s_warp[b][warp] + rank;
+    order[pos] = i;
 }
 }  // namespace
 
 // scratch: 4 * ceil(n_tiles / 1024) + 3 unsigned (the last three receive the number of tiles that cost >= 8x, 4x, 2x the mean); sum: the render kernel's sum of all tile costs (device memory)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
-                      cudaStream_t stream) {
+                      int last_bucket, cudaStream_t stream) {
     if (!n_tiles) return 0;
     const unsigned blocks = (n_tiles + T - 1) / T;
-    tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles);
-    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, scratch + 4 * blocks, n_tiles);
+    tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles, last_bucket);
+    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, scratch + 4 * blocks, n_tiles, last_bucket);
     return (int)cudaGetLastError();
 }
 

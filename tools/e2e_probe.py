@@ -1,0 +1,42 @@
+#!/usr/bin/env python
+"""End-to-end frame time into a pinned host canvas (rtc_render), decoupled copy warps against direct stores.
+usage: python tools/e2e_probe.py [scene w h]   (RTC_COPY_CTAS=0 -> the direct-store path)"""
+import importlib
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tests import scenes  # noqa: E402
+
+
+def main():
+    import numpy as np
+    import torch
+    name = sys.argv[1] if len(sys.argv) > 1 else "dragons"
+    w, h = (int(sys.argv[2]), int(sys.argv[3])) if len(sys.argv) > 3 else (1920, 1080)
+    pkg = importlib.import_module("ray-tracer-challenge_b200")
+    text, assets = scenes.shipped_scene(name)
+    info = pkg.parse_scene(text, assets, w, h)
+    cam, wld = info.camera, info.world
+    host = pkg.pinned_empty((h, w, 3))
+    ref = cam.render(wld).pixels  # pageable: staged
+    for _ in range(8):
+        st = cam.render(wld, out=host).stats
+    assert np.array_equal(host, ref), "pinned canvas differs from the staged frame"
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n = 30
+    k_ms = 0.0
+    for _ in range(n):
+        st = cam.render(wld, out=host).stats
+        k_ms += st.kernel_ms
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / n * 1e3
+    print("%s %dx%d copy_ctas=%s: e2e %.4f ms/frame, kernel %.4f ms, %.1f Mrays/s" % (
+        name, w, h, os.environ.get("RTC_COPY_CTAS", "16 (default)"), ms, k_ms / n, st.rays / ms / 1e3))
+
+
+if __name__ == "__main__":
+    main()
