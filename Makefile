@@ -8,7 +8,7 @@ FMAD ?= false
 EXTRA ?=
 NVFLAGS ?= $(EXTRA) -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=$(FMAD) -Xcompiler -fPIC,-Wall
 INST := $(foreach m,0 1,$(foreach f,0 2 3,$(CSRC)/render_inst_$(m)_$(f).cu))
-SRC := $(INST) $(CSRC)/render_mesh.cu $(CSRC)/render_analytic.cu $(CSRC)/tile_order.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
+SRC := $(INST) $(CSRC)/render_mesh.cu $(CSRC)/render_analytic.cu $(CSRC)/tile_order.cu $(CSRC)/bvh_gpu.cu $(CSRC)/rtc_api.cu $(CSRC)/scene_build.cpp $(CSRC)/bvh.cpp \
        $(CSRC)/host/scene.cpp $(CSRC)/host/scene_parser.cpp $(CSRC)/host/obj.cpp $(CSRC)/host/images.cpp \
        $(CSRC)/host/flatten.cpp $(CSRC)/rtc_renderer.cpp $(CSRC)/host/image_write.cpp
 HDR := $(wildcard $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh $(CSRC)/host/*.hpp include/*.h)

@@ -18,5 +18,9 @@ struct BvhBuild {
 
 // tris: object-space triangle records of the mesh (any order).
 BvhBuild build_bvh(const std::vector<DTri>& tris);
+// The same contract, built on the current CUDA device (bvh_gpu.cu): an LBVH.  Throws std::runtime_error on a CUDA error.
+BvhBuild build_bvh_gpu(const std::vector<DTri>& tris);
+// RTC_BVH=host|gpu|auto (default auto: meshes of >= 65,536 triangles are built on the device when there is one)
+bool bvh_build_on_gpu(size_t n_tris);
 
 }  // namespace rtc

@@ -458,6 +458,8 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if (!out) return fail(RTC_ERR_INVALID, "rtc_scene_create: out is NULL");
     *out = nullptr;
     if (rtc_device_count() <= 0) return fail(RTC_ERR_CUDA, "rtc_scene_create: no CUDA device (there is no CPU fallback)");
+    const int first = g_device.load(), n_dev = g_n_devices.load();
+    CUDA_TRY(cudaSetDevice(first));  // (large meshes build their BVH on it)
     HostScene hs;
     try {
         build_host_scene(blob, nbytes, hs);
@@ -468,7 +470,6 @@ int rtc_scene_create(const void* blob, size_t nbytes, rtc_scene** out) {
     if (hs.csg_max_segments > 16) return fail(RTC_ERR_CAPACITY, "CSG nesting deeper than the segment stack");
     std::vector<uint8_t> stage;
     const SlabLayout o = stage_slab(hs, stage);
-    const int first = g_device.load(), n_dev = g_n_devices.load();
     if (first + n_dev > rtc_device_count()) return fail(RTC_ERR_CUDA, "rtc_scene_create: fewer CUDA devices than rtc_set_devices asked for");
     rtc_scene* s = nullptr;
     int rc = create_on_device(hs, stage, o, first, nullptr, 0, &s);

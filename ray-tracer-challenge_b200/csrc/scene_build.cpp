@@ -2,7 +2,9 @@
 // compilation.  Pure host code (no CUDA calls) so it can be unit-tested without a GPU.
 #include "scene_build.hpp"
 
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -128,7 +130,20 @@ struct CsgCompiler {
 
 }  // namespace
 
+namespace {
+struct Lap {  // RTC_LOAD_TIMING=1: where the set-up time of a scene goes
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    bool on = std::getenv("RTC_LOAD_TIMING") != nullptr;
+    void operator()(const char* what) {
+        auto n = std::chrono::steady_clock::now();
+        if (on) std::fprintf(stderr, "  scene build: %-28s %.3f s\n", what, std::chrono::duration<double>(n - t).count());
+        t = n;
+    }
+};
+}  // namespace
+
 void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
+    Lap lap;
     if (!blob || nbytes < sizeof(rtc_blob_header)) throw std::runtime_error("blob: too small");
     const uint8_t* base = static_cast<const uint8_t*>(blob);
     rtc_blob_header h;
@@ -158,6 +173,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
     copy(roots, h.off_csg_roots, h.n_csg_roots, "csg roots");
     copy(hs.texels, h.off_texels, h.texel_bytes, "texels");
 
+    lap("copy sections");
     // ---- validate every index the kernels will follow --------------------------------------------
     for (auto& m : hs.materials) check_index(m.pattern, h.n_patterns, "material.pattern");
     for (auto& p : hs.patterns) {
@@ -229,6 +245,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         }
     }
 
+    lap("validate");
     // ---- top level: analytic prims, meshes ----------------------------------------------------------
     // A mesh INSTANCE = all non-CSG triangles sharing a world->object matrix and a casts_shadow flag.  Instances whose
     // object-space triangles (positions, edges, normals, flat/smooth) are the same multiset share ONE geometry: one
@@ -313,6 +330,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         }
         for (auto& j : jobs) j.get();
     }
+    lap("instances, canonical order");
     struct Geometry {
         size_t first_inst;
         int32_t root = 0;  // BvhNode index
@@ -335,6 +353,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             geoms.push_back(Geometry{i});
         }
     }
+    lap("match geometries");
     hs.bvh_max_depth = 0;
     // the geometries are independent: one builder thread each
     std::vector<std::vector<DTri>> gtris(geoms.size());
@@ -353,9 +372,11 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
             d.pad = 0;
         }
         const std::vector<DTri>* tris = &v;
-        builds.push_back(std::async(geoms.size() > 1 ? std::launch::async : std::launch::deferred,
-                                    [tris] { return build_bvh(*tris); }));
+        // large meshes: LBVH on the device (bvh_gpu.cu), built when its turn comes, on the caller's thread and device
+        if (bvh_build_on_gpu(v.size())) builds.push_back(std::async(std::launch::deferred, [tris] { return build_bvh_gpu(*tris); }));
+        else builds.push_back(std::async(geoms.size() > 1 ? std::launch::async : std::launch::deferred, [tris] { return build_bvh(*tris); }));
     }
+    lap("gather triangles");
     for (size_t g = 0; g < geoms.size(); g++) {
         BvhBuild b = builds[g].get();
         geoms[g].root = (int32_t)hs.bvh.size();
@@ -373,6 +394,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
         hs.tris.insert(hs.tris.end(), b.tris.begin(), b.tris.end());
         if (b.max_depth > hs.bvh_max_depth) hs.bvh_max_depth = b.max_depth;
     }
+    lap("geometries + BVH build");
     hs.n_geometries = (int)geoms.size();
     for (const Instance& in : insts) {
         const Geometry& G = geoms[(size_t)in.geometry];
@@ -405,6 +427,7 @@ void build_host_scene(const void* blob, size_t nbytes, HostScene& hs) {
     // leaves are encoded on the traversal stack as ~((first << 3) | count)  (rt_trace.cuh trace_meshes)
     if (hs.tris.size() >= (size_t(1) << 27)) throw std::runtime_error("more than 2^27 mesh triangles");
 
+    lap("instances -> meshes");
     // ---- CSG programs ------------------------------------------------------------------------------
     CsgCompiler cc{hs.nodes, children, hs.csg_prog};
     for (int32_t r : roots) {

@@ -556,3 +556,30 @@ def test_frame_shared_tile_by_tile_is_the_same_frame(pkg, n):
     camera.render_device_frame(worlds[0], frame.data_ptr())
     torch.cuda.synchronize()
     assert np.array_equal(frame.cpu().numpy(), want.pixels)
+
+
+@pytest.mark.parametrize("name", ["teapot", "dragons", "nefertiti", "mesh"])
+def test_gpu_built_and_host_built_bvh_give_the_same_frame(pkg, tmp_path, name):
+    """the BVH of a mesh built on the device (LBVH, bvh_gpu.cu; RTC_BVH=gpu) and on the host (binned
+    SAH, bvh.cpp; RTC_BVH=host).  Both trees only cull with conservative boxes, hits and ties are decided by the f64
+    test and the leaf order: the same frame and the same ray counts, bit for bit."""
+    if name == "mesh":
+        scenes.write_mesh_obj(str(tmp_path / "torus.obj"), smooth=True, groups=False)
+        text, assets, (w, h) = scenes.mesh_scene("torus.obj"), str(tmp_path), (200, 120)
+    else:
+        s = scenes.shipped_scene(name)
+        if s is None:
+            pytest.skip("reference assets not staged")
+        text, assets, (w, h) = s[0], s[1], (320, 200)
+    out = {}
+    try:
+        for mode in ("host", "gpu"):
+            os.environ["RTC_BVH"] = mode  # read when the scene is created
+            info = pkg.parse_scene(text, assets, w, h)
+            c = info.camera.render(info.world)
+            out[mode] = (c.pixels.copy(), (c.stats.primary_rays, c.stats.shadow_rays, c.stats.secondary_rays))
+            info.world.close()
+    finally:
+        os.environ.pop("RTC_BVH", None)
+    assert out["host"][0].any()
+    assert np.array_equal(out["host"][0], out["gpu"][0]) and out["host"][1] == out["gpu"][1]
