@@ -33,6 +33,7 @@ std::shared_ptr<Image> decode_png(const std::string& bytes, const std::string& n
     const unsigned char* end = (const unsigned char*)bytes.data() + bytes.size();
     uint32_t w = 0, h = 0;
     int depth = 0, ctype = 0, interlace = 0;
+    bool have_ihdr = false;
     std::string idat;
     std::vector<unsigned char> palette;
     while (p + 12 <= end) {
@@ -40,7 +41,10 @@ std::shared_ptr<Image> decode_png(const std::string& bytes, const std::string& n
         const char* type = (const char*)p + 4;
         const unsigned char* data = p + 8;
         if (data + len + 4 > end) throw std::runtime_error("png: truncated chunk");
+        if (!have_ihdr && std::memcmp(type, "IHDR", 4)) throw std::runtime_error("png: IHDR is not the first chunk");
         if (!std::memcmp(type, "IHDR", 4)) {
+            if (len != 13 || have_ihdr) throw std::runtime_error("png: bad IHDR");
+            have_ihdr = true;
             w = be32(data);
             h = be32(data + 4);
             depth = data[8];
@@ -55,7 +59,12 @@ std::shared_ptr<Image> decode_png(const std::string& bytes, const std::string& n
         }
         p = data + len + 4;
     }
+    if (!have_ihdr) throw std::runtime_error("png: no IHDR");
+    // 16-bit samples and Adam7 interlacing are not decoded (the reference's decoder, zigimg, is not vendored: what it
+    // accepts beyond the shipped 8-bit RGB, non-interlaced textures was not checked)
     if (depth != 8 || interlace != 0) throw std::runtime_error("png: only 8-bit non-interlaced supported");
+    // sizes come from the file: nothing below may wrap (1 <= w, h and w * h * channels <= 2^31)
+    if (w == 0 || h == 0 || (uint64_t)w * h > (uint64_t(1) << 29)) throw std::runtime_error("png: image size out of range");
     int ch = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
     if (!ch) throw std::runtime_error("png: bad colour type");
     size_t stride = (size_t)w * ch;

@@ -67,53 +67,41 @@ __device__ __forceinline__ void pk_st(double* pk, int k, V3 v) {
 }
 #define PK(k) pk[(k) * RTC_BLOCK]
 
-// The copy warps of a frame that goes to mapped host memory (RenderParams::copy_out): take the finished tiles in the
-// order they are announced and move each to the host canvas.  A tile is 4 rows of 8 pixels x 3 doubles = 4 x 192
-// contiguous bytes: lane l moves doubles l, l + 32, l + 64 of the tile's 96, so every store instruction covers whole rows.
-// A warp claims RTC_COPY_BATCH tiles at a time -- lanes 0 .. BATCH-1 each wait for one announcement, then the loads of all
-// of them are in flight together: one tile at a time a warp is a chain of L2 round trips (claim, poll, load: ~2.5 us per
-// 768 bytes, measured: 64 copy warps moved 19 GB/s).
-#ifndef RTC_COPY_BATCH
-#define RTC_COPY_BATCH 8
-#endif
-__device__ __forceinline__ void copy_finished_tiles(const RenderParams& P) {
+// The copy warps of a frame that goes to mapped host memory (RenderParams::copy_out): take the finished rows of tiles in
+// the order they are announced and move each -- RTC_TILE_H scanlines, one contiguous run of hsize x 3 x RTC_TILE_H doubles
+// -- to the host canvas, 32 lanes x 8 bytes side by side, several loads in flight per lane.  (Tile by tile, 192 bytes at
+// a time, the same warps moved a 1080p frame at 43 GB/s and a 2160p frame at 21 GB/s: the host side wants long runs.)
+__device__ __forceinline__ void copy_finished_rows(const RenderParams& P) {
     const unsigned lane = threadIdx.x & 31u;
+    const unsigned long long row_doubles = P.cam.hsize * 3ull;
     for (;;) {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(P.copy_ctl + 1, (unsigned)RTC_COPY_BATCH) + 1u;  // (the counters start at 0xffffffff: one memset sets up list and counters)
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= P.copy_tiles) return;
-        unsigned mine = 0xffffffffu;
-        if (lane < RTC_COPY_BATCH && base + lane < P.copy_tiles) {
-            volatile unsigned* slot = P.done_list + base + lane;
+        unsigned idx = 0, row = 0xffffffffu;
+        if (lane == 0) idx = atomicAdd(P.copy_ctl + 1, 1u) + 1u;  // (the cursors start at 0xffffffff: one memset sets everything up)
+        idx = __shfl_sync(0xffffffffu, idx, 0);
+        if (idx >= P.copy_rows) return;
+        if (lane == 0) {
+            volatile unsigned* slot = P.done_list + idx;
             unsigned spins = 0;
-            while ((mine = *slot) == 0xffffffffu && ++spins < (1u << 22)) __nanosleep(200);  // (~1 s: a frame takes milliseconds)
-            if (mine == 0xffffffffu) atomicOr(P.counters + 4, (unsigned long long)ERR_COPY);  // never announced: flag the frame, do not hang
-            __threadfence();  // the tile's pixels were written before it was announced
+            while ((row = *slot) == 0xffffffffu && ++spins < (1u << 22)) __nanosleep(500);  // (~2 s: a frame takes milliseconds)
+            if (row == 0xffffffffu) atomicOr(P.counters + 4, (unsigned long long)ERR_COPY);  // never announced: flag the frame, do not hang
+            __threadfence();  // the row's pixels were written before it was announced
         }
-        __syncwarp();
-        double v[RTC_COPY_BATCH][3];
-        unsigned long long at[RTC_COPY_BATCH][3];
+        row = __shfl_sync(0xffffffffu, row, 0);
+        if (row == 0xffffffffu) return;
+        const unsigned long long y0 = (unsigned long long)row * RTC_TILE_H;
+        const unsigned long long y1 = y0 + RTC_TILE_H < P.cam.vsize ? y0 + RTC_TILE_H : P.cam.vsize;
+        const unsigned long long first = y0 * row_doubles, last = y1 * row_doubles;
+        const double* __restrict__ src = P.out;
+        double* __restrict__ dst = P.copy_out;
+        unsigned long long i = first + lane;
+        for (; i + 7ull * 32ull < last; i += 8ull * 32ull) {
+            double v[8];
 #pragma unroll
-        for (int j = 0; j < RTC_COPY_BATCH; j++) {
-            const unsigned tile = __shfl_sync(0xffffffffu, mine, j);
-            const unsigned long long px0 = (unsigned long long)(tile % P.tiles_x) * RTC_TILE_W, y0 = (unsigned long long)(tile / P.tiles_x) * RTC_TILE_H;
+            for (int k = 0; k < 8; k++) v[k] = __ldcg(src + i + 32ull * k);
 #pragma unroll
-            for (unsigned k = 0; k < 3; k++) {
-                const unsigned e = lane + 32u * k, row = e / (3u * RTC_TILE_W), col = e % (3u * RTC_TILE_W);  // double `col` of tile row `row`
-                const unsigned long long y = y0 + row, px = px0 + col / 3u;
-                at[j][k] = ~0ull;
-                if (tile != 0xffffffffu && y < P.cam.vsize && px < P.cam.hsize) {
-                    at[j][k] = (y * P.cam.hsize + px0) * 3ull + col;
-                    v[j][k] = __ldcg(P.out + at[j][k]);
-                }
-            }
+            for (int k = 0; k < 8; k++) dst[i + 32ull * k] = v[k];
         }
-#pragma unroll
-        for (int j = 0; j < RTC_COPY_BATCH; j++)
-#pragma unroll
-            for (unsigned k = 0; k < 3; k++)
-                if (at[j][k] != ~0ull) P.copy_out[at[j][k]] = v[j][k];
+        for (; i < last; i += 32ull) dst[i] = __ldcg(src + i);
     }
 }
 
@@ -165,7 +153,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     constexpr bool MIXED = LPP == 0;
     if constexpr (LPP == 1) {  // (a decoupled host canvas is a whole frame with one lane per pixel)
         if (P.copy_out && blockIdx.x < P.copy_ctas) {
-            copy_finished_tiles(P);
+            copy_finished_rows(P);
             return;
         }
     }
@@ -265,9 +253,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         atomicAdd(reinterpret_cast<unsigned long long*>(cp + P.cost_tiles), (unsigned long long)cost);  // the mean of the frame (tile_order.cu)
                     }
                 }
-                if (LPP == 1 && P.copy_out) {  // for the copy warps (copy_finished_tiles): where the tile lies in the frame
-                    __threadfence();
-                    P.done_list[atomicAdd(P.copy_ctl, 1u) + 1u] = (unsigned)PK(PK_SPARE + 2);
+                if (LPP == 1 && P.copy_out) {  // for the copy warps (copy_finished_rows): one more tile of its row is done
+                    const unsigned row = (unsigned)PK(PK_SPARE + 2) / P.tiles_x;
+                    __threadfence();  // the tile's pixels before the count
+                    if (atomicAdd(P.row_count + row, 1u) + 2u == P.tiles_x) {  // (counts start at 0xffffffff) the row's last tile
+                        __threadfence();
+                        P.done_list[atomicAdd(P.copy_ctl, 1u) + 1u] = row;
+                    }
                 }
                 PK(PK_SPARE) = -1.0;
             }

@@ -80,13 +80,16 @@ struct RenderParams {
     unsigned int deal_n, deal_rank;
     unsigned int deal_shift;  // the order is dealt in runs of 1 << deal_shift consecutive entries (neighbouring tiles stay with one renderer)
     // Frame for a canvas in mapped HOST memory, decoupled from the link: the render warps store their pixels into `out`
-    // in device memory and announce every finished tile in done_list[]; the warps of the first copy_ctas CTAs do nothing
-    // but wait for announcements and move finished tiles to copy_out over PCIe in full 192-byte rows.  The link is busy
-    // from the first finished tile on and no render warp ever waits for it (render_kernel.cuh copy_finished_tiles).
+    // in device memory and count the finished tiles of every ROW of tiles; a row that is complete is announced in
+    // done_list[], and the warps of the first copy_ctas CTAs do nothing but wait for announcements and move finished
+    // rows -- RTC_TILE_H full scanlines, contiguous -- to copy_out over PCIe.  The link is busy from the first finished
+    // row on, no render warp ever waits for it, and the host canvas is written front to back in long runs
+    // (render_kernel.cuh copy_finished_rows).
     double* copy_out;          // NULL: off
-    unsigned int* done_list;   // [copy_tiles] tiles in the order they were finished (0xffffffff: not yet)
-    unsigned int* copy_ctl;    // [0] tiles announced, [1] tiles taken by copy warps
-    unsigned int copy_ctas, copy_tiles;
+    unsigned int* done_list;   // [copy_rows] rows of tiles in the order they were finished (0xffffffff: not yet)
+    unsigned int* copy_ctl;    // [0] rows announced, [1] rows taken by copy warps (both start at 0xffffffff)
+    unsigned int* row_count;   // [copy_rows] finished tiles of the row (starts at 0xffffffff)
+    unsigned int copy_ctas, copy_rows;
     const unsigned int* heavy_tiles;  // device word: how many leading entries of tile_order cost >= 8x the mean (LPP == 0)
     unsigned long long* counters;  // [0] next item, [1] primary, [2] shadow, [3] secondary, [4] error bits, [5] culled shadow rays
 };

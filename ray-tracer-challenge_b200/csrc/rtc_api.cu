@@ -668,6 +668,7 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (part->n_parts == 0 || part->part >= part->n_parts || part->tile_rows == 0)
         return fail(RTC_ERR_INVALID, "render: bad partition");
     CUDA_TRY(cudaSetDevice(s->device));
+    s->last_copied = false;
     // a free ring slot: the oldest frame nobody fetched is resolved (its time still counts for the kernel choice) and dropped
     if (s->seq_next - s->seq_pop == (uint64_t)rtc_scene::kRing) {
         const int old = (int)(s->seq_pop % rtc_scene::kRing);
@@ -832,25 +833,27 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     // A whole frame for a mapped host canvas, one lane per pixel: rendered into device memory, moved by copy warps.
     static const unsigned copy_ctas = [] {
         const char* e = std::getenv("RTC_COPY_CTAS");
-        int v = e ? std::atoi(e) : 8;  // measured on B200, dragons 1080p e2e ms: 2 CTAs 2.98, 4: 1.51, 8: 1.21, 12: 1.21, 16: 1.63
-        return (unsigned)(v >= 0 && v <= 64 ? v : 8);
+        int v = e ? std::atoi(e) : 4;  // measured on B200, dragons 1080p e2e ms per frame: 4 CTAs 1.27, 8: 1.28, 16: 1.29 (direct stores: 1.54)
+        return (unsigned)(v >= 0 && v <= 64 ? v : 4);
     }();
-    s->last_copied = false;
     if (tg.copy_out && tg.rgb && !dealt && P.n_parts == 1 && lpp == 1 && copy_ctas > 0 && (int)copy_ctas * 2 <= s->grid) {
-        if (s->done_cap < n_tiles) {
+        // per row of tiles: a counter of finished tiles; the list of finished rows; the two cursors -- all set to 0xffffffff
+        const size_t n_rows = n_tile_rows, words = 2 * n_rows + 2;
+        if (s->done_cap < words) {
             CUDA_TRY(cudaStreamSynchronize(stream));
             if (s->d_done) cudaFree(s->d_done);
             s->d_done = nullptr;
             s->done_cap = 0;
-            CUDA_TRY(cudaMalloc(&s->d_done, (n_tiles + 2) * sizeof(unsigned)));
-            s->done_cap = n_tiles;
+            CUDA_TRY(cudaMalloc(&s->d_done, words * sizeof(unsigned)));
+            s->done_cap = words;
         }
-        CUDA_TRY(cudaMemsetAsync(s->d_done, 0xff, (n_tiles + 2) * sizeof(unsigned), stream));
+        CUDA_TRY(cudaMemsetAsync(s->d_done, 0xff, words * sizeof(unsigned), stream));
         P.copy_out = tg.copy_out;
         P.done_list = s->d_done;
-        P.copy_ctl = s->d_done + n_tiles;
+        P.copy_ctl = s->d_done + n_rows;
+        P.row_count = s->d_done + n_rows + 2;
         P.copy_ctas = copy_ctas;
-        P.copy_tiles = (unsigned)n_tiles;
+        P.copy_rows = (unsigned)n_rows;
         s->last_copied = true;
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
@@ -876,7 +879,6 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         if (s->order_cap < n_tiles) {  // the arrays that are never shared: bucket counts, the permutation
             CUDA_TRY(cudaStreamSynchronize(stream));
             if (s->d_scratch) cudaFree(s->d_scratch);
-    if (s->d_done) cudaFree(s->d_done);
             if (s->d_tile_order) cudaFree(s->d_tile_order);
             s->d_scratch = s->d_tile_order = nullptr;
             s->order_cap = 0;
@@ -1197,7 +1199,12 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
             const char* e = std::getenv("RTC_COPY_CTAS");
             return !(e && std::atoi(e) == 0);
         }();
-        if (decouple && whole && s->replicas.empty()) {
+        // ... where moving the frame is a large part of it: a frame whose kernel takes more than twice as long as the
+        // link needs for its bytes (cover.json 1080p: 2.1 ms against 0.95) gains nothing from copy warps and loses their
+        // CTAs -- there the render warps store into the canvas themselves, as partitions and replicated scenes do
+        const double link_ms = (double)cam->vsize * cam->hsize * 24.0 / 52e6;  // ~52 GB/s measured for SM-written host memory
+        const bool worth = s->best_ms[0] < 0.0f || link_ms >= 0.5 * s->best_ms[0];
+        if (decouple && worth && whole && s->replicas.empty()) {
             // whole frame, one device: rendered into device memory in cost order at full speed while copy warps move
             // every finished tile to the canvas (enqueue_frame); a frame the library renders another way is copied
             int rc = ensure_frame(s, (size_t)cam->vsize * cam->hsize * 3 * sizeof(double) + 16);

@@ -34,8 +34,11 @@ def main():
         k_ms += st.kernel_ms
     torch.cuda.synchronize()
     ms = (time.perf_counter() - t0) / n * 1e3
-    print("%s %dx%d copy_ctas=%s: e2e %.4f ms/frame, kernel %.4f ms, %.1f Mrays/s" % (
-        name, w, h, os.environ.get("RTC_COPY_CTAS", "16 (default)"), ms, k_ms / n, st.rays / ms / 1e3))
+    host[:] = 0.0  # the steady-state path really delivers the frame
+    st = cam.render(wld, out=host).stats
+    assert np.array_equal(host, ref), "steady-state frame did not reach the pinned canvas"
+    print("%s %dx%d copy_ctas=%s: e2e %.4f ms/frame, kernel %.4f ms (%s), %.1f Mrays/s" % (
+        name, w, h, os.environ.get("RTC_COPY_CTAS", "default"), ms, k_ms / n, ("mega", "wave", "mixed")[st.kernel], st.rays / ms / 1e3))
 
 
 if __name__ == "__main__":
