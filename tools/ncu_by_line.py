@@ -23,8 +23,13 @@ BY = "inner"
 def line_table(kernel_substr):
     """offset -> (file, line) for the first kernel whose mangled name contains kernel_substr."""
     tmp = tempfile.mkdtemp()
-    # (the last, merged image has a name longer than a file name may be: cuobjdump fails on it after extracting the per-source ones)
-    subprocess.run(["cuobjdump", "-xelf", "all", LIB], cwd=tmp, check=False, capture_output=True)
+    # image by image: the merged image's name (all sources joined) is longer than a file name may be, and
+    # `cuobjdump -xelf all` gives up on it before extracting the per-source ones
+    listing = subprocess.run(["cuobjdump", "-lelf", LIB], capture_output=True, text=True).stdout
+    for ln in listing.splitlines():
+        name = ln.split(":", 1)[-1].strip()
+        if name.endswith(".cubin") and len(name) < 200:
+            subprocess.run(["cuobjdump", "-xelf", name, LIB], cwd=tmp, check=False, capture_output=True)
     table, lines_src = {}, {}
     for f in sorted(os.listdir(tmp)):
         if not f.endswith(".cubin"):
