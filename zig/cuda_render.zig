@@ -25,6 +25,14 @@ pub const c = @cImport({
 
 const T = f64;
 
+/// The reference's only parallelism knob is `n_threads` (lib.zig:157-164; camera.zig:88-97 hands one row to each
+/// worker).  Its twin here: how many GPUs of this process render a frame.  Call before the first `render`; scenes
+/// created afterwards are built once and replicated device to device, and every frame is split over the devices
+/// (include/rtc_b200.h rtc_set_devices).  Nothing else in this file changes.
+pub fn setDevices(n_gpus: usize) !void {
+    if (c.rtc_set_devices(@intCast(n_gpus)) != 0) return error.CudaRenderFailed;
+}
+
 fn Section(comptime R: type) type {
     return std.ArrayList(R);
 }
