@@ -479,7 +479,7 @@ def main():
             return camera.render(wld, DEPTH, None, out=host if canvas is None else canvas).stats
         if shared is not None:  # the same public call on every rank, rows of its partition, then a barrier
             st = camera.render(e2e_world, DEPTH, part, out=shared.array).stats
-            dist.barrier()
+            shared.barrier()  # every rank's rows are in host memory
             return st
         step_device()  # render + exchange on the GPUs, then the assembled frame goes to the host on rank 0
         st = (drain() or [None])[-1]

@@ -88,9 +88,12 @@ __device__ __forceinline__ void copy_finished_rows(const RenderParams& P) {
         }
         row = __shfl_sync(0xffffffffu, row, 0);
         if (row == 0xffffffffu) return;
-        const unsigned long long y0 = (unsigned long long)row * RTC_TILE_H;
-        const unsigned long long y1 = y0 + RTC_TILE_H < P.cam.vsize ? y0 + RTC_TILE_H : P.cam.vsize;
-        const unsigned long long first = y0 * row_doubles, last = y1 * row_doubles;
+        // `row` counts the rows of tiles of this PARTITION (packed rows pr0 ...); its scanlines lie together in the frame
+        // as long as tile_rows is a multiple of RTC_TILE_H (the host checks): y as in the refill above
+        const unsigned long long pr0 = (unsigned long long)row * RTC_TILE_H;
+        const unsigned long long pr1 = pr0 + RTC_TILE_H < P.rows ? pr0 + RTC_TILE_H : P.rows;
+        const unsigned long long y0 = ((pr0 / P.tile_rows) * P.n_parts + P.part) * P.tile_rows + pr0 % P.tile_rows;
+        const unsigned long long first = y0 * row_doubles, last = (y0 + (pr1 - pr0)) * row_doubles;
         const double* __restrict__ src = P.out;
         double* __restrict__ dst = P.copy_out;
         unsigned long long i = first + lane;

@@ -836,7 +836,8 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         int v = e ? std::atoi(e) : 4;  // measured on B200, dragons 1080p e2e ms per frame: 4 CTAs 1.27, 8: 1.28, 16: 1.29 (direct stores: 1.54)
         return (unsigned)(v >= 0 && v <= 64 ? v : 4);
     }();
-    if (tg.copy_out && tg.rgb && !dealt && P.n_parts == 1 && lpp == 1 && copy_ctas > 0 && (int)copy_ctas * 2 <= s->grid) {
+    if (tg.copy_out && tg.rgb && tg.full_frame && !dealt && (P.n_parts == 1 || P.tile_rows % RTC_TILE_H == 0) && lpp == 1 && copy_ctas > 0 &&
+        (int)copy_ctas * 2 <= s->grid) {
         // per row of tiles: a counter of finished tiles; the list of finished rows; the two cursors -- all set to 0xffffffff
         const size_t n_rows = n_tile_rows, words = 2 * n_rows + 2;
         if (s->done_cap < words) {
@@ -1158,6 +1159,23 @@ static int scatter_rows(const rtc_camera* cam, const rtc_partition* part, const 
     return RTC_OK;
 }
 
+// The rows of a partition from a frame-sized device buffer to the same places of a frame-sized host buffer.
+static int copy_partition_in_place(const rtc_camera* cam, const rtc_partition* part, const void* d_src, void* h_dst, size_t px_bytes) {
+    const size_t row_bytes = (size_t)cam->hsize * px_bytes;
+    const uint64_t tr = part->tile_rows, n_tiles = (cam->vsize + tr - 1) / tr;
+    if (part->part >= n_tiles) return RTC_OK;
+    const uint64_t mine = (n_tiles - part->part + part->n_parts - 1) / part->n_parts;
+    const uint64_t last = part->part + (mine - 1) * part->n_parts;
+    const bool ragged = (last + 1) * tr > cam->vsize;
+    const uint64_t full = ragged ? mine - 1 : mine;
+    const size_t tile_bytes = (size_t)tr * row_bytes, first = (size_t)part->part * tile_bytes, pitch = (size_t)part->n_parts * tile_bytes;
+    if (full) CUDA_TRY(cudaMemcpy2D((char*)h_dst + first, pitch, (const char*)d_src + first, pitch, tile_bytes, full, cudaMemcpyDeviceToHost));
+    if (ragged)
+        CUDA_TRY(cudaMemcpy((char*)h_dst + (size_t)last * tile_bytes, (const char*)d_src + (size_t)last * tile_bytes,
+                            (size_t)(cam->vsize - last * tr) * row_bytes, cudaMemcpyDeviceToHost));
+    return RTC_OK;
+}
+
 // Pinned, device-mapped host memory for canvases (rtc_b200.h).
 void* rtc_host_alloc(size_t nbytes) {
     void* p = nullptr;
@@ -1202,12 +1220,17 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
         // ... where moving the frame is a large part of it: a frame whose kernel takes more than twice as long as the
         // link needs for its bytes (cover.json 1080p: 2.1 ms against 0.95) gains nothing from copy warps and loses their
         // CTAs -- there the render warps store into the canvas themselves, as partitions and replicated scenes do
-        const double link_ms = (double)cam->vsize * cam->hsize * 24.0 / 52e6;  // ~52 GB/s measured for SM-written host memory
+        const uint64_t my_rows = rtc_partition_rows(cam->vsize, part);
+        const double link_ms = (double)my_rows * cam->hsize * 24.0 / 52e6;  // ~52 GB/s measured for SM-written host memory
         const bool worth = s->best_ms[0] < 0.0f || link_ms >= 0.5 * s->best_ms[0];
-        if (decouple && worth && whole && s->replicas.empty()) {
-            // whole frame, one device: rendered into device memory in cost order at full speed while copy warps move
-            // every finished tile to the canvas (enqueue_frame); a frame the library renders another way is copied
-            int rc = ensure_frame(s, (size_t)cam->vsize * cam->hsize * 3 * sizeof(double) + 16);
+        const bool rows_ok = whole || part->tile_rows % RTC_TILE_H == 0;  // a row of tiles lies together in the frame
+        if (decouple && worth && rows_ok && s->replicas.empty()) {
+            // rendered into device memory (a frame-sized staging buffer, pixels at their frame positions) in cost order at
+            // full speed while copy warps move every finished row of tiles to the canvas (enqueue_frame); a frame the
+            // library renders another way (wavefront, several lanes per pixel) is copied afterwards.  A partition of the
+            // frame works the same way: N processes, each with its own link, fill one shared pinned canvas.
+            const size_t frame_bytes = (size_t)cam->vsize * cam->hsize * 3 * sizeof(double);
+            int rc = ensure_frame(s, frame_bytes + 16);
             if (rc) return rc;
             Target tg;
             tg.rgb = s->d_frame;
@@ -1215,8 +1238,11 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
             tg.copy_out = static_cast<double*>(mapped);
             rc = render_frame(s, cam, max_depth, part, tg, 0, true, stats);
             if (rc || s->last_copied) return rc;
-            CUDA_TRY(cudaMemcpy(rgb_out, s->d_frame, (size_t)cam->vsize * cam->hsize * 3 * sizeof(double), cudaMemcpyDeviceToHost));
-            return RTC_OK;
+            if (whole) {
+                CUDA_TRY(cudaMemcpy(rgb_out, s->d_frame, frame_bytes, cudaMemcpyDeviceToHost));
+                return RTC_OK;
+            }
+            return copy_partition_in_place(cam, part, s->d_frame, rgb_out, 3 * sizeof(double));
         }
         Target tg;
         tg.rgb = static_cast<double*>(mapped);

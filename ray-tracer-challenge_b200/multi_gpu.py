@@ -132,7 +132,7 @@ class SharedHostFrame:
         nbytes = height * width * 3 * 8
         name = [None]
         if rank == 0:
-            self.shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            self.shm = shared_memory.SharedMemory(create=True, size=nbytes + 4096)  # + one arrival counter per rank
             name[0] = self.shm.name
         if world > 1:
             dist.broadcast_object_list(name, src=0, group=group)
@@ -144,8 +144,11 @@ class SharedHostFrame:
             except Exception:  # noqa: BLE001
                 pass
         self.array = np.ndarray((height, width, 3), dtype=np.float64, buffer=self.shm.buf)
+        self.flags = np.ndarray((world,), dtype=np.int64, buffer=self.shm.buf, offset=nbytes)
+        self.round = 0
         if rank == 0:
             self.array[:] = 0.0
+            self.flags[:] = 0
         self.registered = False
         if register:
             rt = torch.cuda.cudart()
@@ -157,11 +160,21 @@ class SharedHostFrame:
         if world > 1:
             dist.barrier(group=group)
 
+    def barrier(self):
+        """Host-side barrier of the ranks sharing the canvas: every rank publishes how many frames it has delivered in
+        its own slot of the segment and waits until all slots have caught up (microseconds; an NCCL barrier is a kernel
+        launch and a stream synchronisation per rank).  Call after Camera.render has returned (its frame rows are in)."""
+        self.round += 1
+        self.flags[self.rank] = self.round
+        while int(self.flags.min()) < self.round:
+            pass
+
     def close(self):
         if self.registered:
             torch.cuda.cudart().cudaHostUnregister(self.array.ctypes.data)
             self.registered = False
         self.array = None
+        self.flags = None
         self.shm.close()
         if self.rank == 0:
             self.shm.unlink()

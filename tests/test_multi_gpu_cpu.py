@@ -75,9 +75,11 @@ def _shared_worker(rank, world, port, width, height, tile_rows, out_path):
         for y in mg.partition_rows(height, tile_rows, rank, world):  # stand-in for the render of this rank's rows
             f.array[y, :, 0] = y + 1
             f.array[y, :, 1] = rank
-        dist.barrier()
+        f.barrier()  # the canvas's own shared-memory barrier (what bench.py's N-GPU end-to-end leg ends a frame with)
         if rank == 0:
             torch.save(torch.from_numpy(f.array.copy()), out_path)
+        for _ in range(3):
+            f.barrier()
         dist.barrier()
         f.close()
     finally:
