@@ -117,6 +117,25 @@ int rtc_render_device_frame(rtc_scene* scene, const rtc_camera* cam, int max_dep
 int rtc_render_device_async(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                             double* d_frame, void* stream);
 int rtc_stats_fetch(rtc_scene* scene, rtc_stats* stats_out, uint32_t max_frames, uint32_t* n_out);
+/* rtc_render_device for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  The whole frame,
+ * hsize*vsize*3 doubles, into caller-owned device memory d_rgb, by the megakernel, bit-identical to rtc_render_device's.
+ * The call makes no cudaMalloc / cudaFree / allocating library call: the kernel's scratch (ray counters, per-tile costs,
+ * the tile order made from the previous call's costs) lives in a fixed array in the library's device image -- 3.1 MB that
+ * every GPU which loads the library holds until the process exits.  LIMIT: frames of at most rtc_static_max_tiles() =
+ * 262,144 tiles of 8x4 pixels (3840x2160 fits); larger frames are refused with RTC_ERR_INVALID.
+ * The array is shared by EVERY call on a device and keeps the last call's contents (that is how a re-render of a view
+ * gets its tile order); the call clears what must start at zero.  Calls that overlap on the GPU (different streams without
+ * an event between them, or different host threads) race on it: one call at a time per device.  It is independent of the
+ * scratch of the other entry points, which may be used on the same scene in between.
+ * stats != NULL: the call waits for the frame and reports rays, kernel time and capacity errors like rtc_render_device.
+ * stats == NULL: the work (two memsets, the render kernel and, when the call before recorded tile costs, the two order kernels) is only
+ * put on `stream`;
+ * nothing is synchronised and capacity errors are not reported.  Replicated scenes (rtc_set_devices) render on their
+ * first device. */
+uint64_t rtc_static_max_tiles(void);
+int rtc_render_device_static(rtc_scene* scene, const rtc_camera* cam, int max_depth, double* d_rgb, void* stream,
+                             rtc_stats* stats);
 /* One frame shared by several renderers, one PROCESS per GPU (rank r of n_ranks; the layout torchrun / MPI hosts use).
  * Instead of fixed row partitions the renderers take the tiles of ONE order -- the frame's 8x4-pixel tiles sorted into
  * buckets by what they cost in the previous frame -- in turn: entry r, r + n, r + 2n, ...: every renderer gets its

@@ -72,7 +72,8 @@ class rtc_stats(ctypes.Structure):
 # every symbol include/rtc_b200.h declares
 EXPORTS = ["rtc_last_error", "rtc_device_count", "rtc_set_device", "rtc_set_devices", "rtc_render_device_async", "rtc_stats_fetch", "rtc_tile_share_words", "rtc_scene_share_tiles", "rtc_blob_inspect", "rtc_scene_create", "rtc_scene_destroy",
            "rtc_render", "rtc_render_rgba8", "rtc_render_device", "rtc_render_device_frame", "rtc_partition_rows", "rtc_load_scene_json",
-           "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png"]
+           "rtc_blob_free", "rtc_camera_look_at", "rtc_host_alloc", "rtc_host_free", "rtc_canvas_ppm", "rtc_write_png",
+           "rtc_static_max_tiles", "rtc_render_device_static"]
 # include/rtc_renderer.h: the twelve exports of the reference's own library (src/lib.zig:233-309) + two of ours
 RENDERER_EXPORTS = ["startInitRenderer", "tryFinishInitRenderer", "initRendererIsOk", "initRendererGetPixels",
                     "initRendererGetWidth", "initRendererGetHeight", "initRendererGetErr", "deinitRenderer",
@@ -110,6 +111,8 @@ def lib():
     L.rtc_render_rgba8.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_device.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_device_frame.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
+    L.rtc_static_max_tiles.restype = ctypes.c_uint64
+    L.rtc_render_device_static.argtypes = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, vp, vp, ctypes.POINTER(rtc_stats)]
     L.rtc_partition_rows.argtypes = [ctypes.c_uint64, ctypes.POINTER(rtc_partition)]
     L.rtc_partition_rows.restype = ctypes.c_uint64
     L.rtc_load_scene_json.argtypes = [cp, cp, ctypes.c_long, ctypes.c_long, ctypes.POINTER(vp),
@@ -373,6 +376,15 @@ class Camera:
                                              ctypes.c_void_p(d_frame_ptr), ctypes.c_void_p(stream), ctypes.byref(st)))
         return st
 
+
+    def render_device_static(self, world, d_ptr, max_depth=5, stream=0, wait=True):
+        """rtc_render_device_static: the whole frame into device memory at d_ptr WITHOUT any allocation (scratch in a
+        fixed array of the library's device image; frames of at most rtc_static_max_tiles() 8x4-pixel tiles).
+        wait=False only puts the work on `stream` and returns None."""
+        st = rtc_stats() if wait else None
+        _check(lib().rtc_render_device_static(world._h, ctypes.byref(self.c), max_depth, ctypes.c_void_p(d_ptr),
+                                              ctypes.c_void_p(stream), ctypes.byref(st) if wait else None))
+        return st
 
     def render_device_async(self, world, d_frame_ptr, max_depth=5, partition=None, stream=0):
         """render_device_frame without the wait: the frame is put on `stream`; World.fetch_stats() collects the statistics."""

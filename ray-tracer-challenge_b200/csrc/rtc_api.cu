@@ -1326,3 +1326,157 @@ int rtc_camera_look_at(rtc_camera* cam, const double from[3], const double to[3]
 }
 
 }  // extern "C"
+
+// ---- a render call that allocates nothing ---------------------------------------------------------------------------
+// (No counterpart in the reference; added for callers that cannot call cudaMalloc:
+// code under CUDA graph capture, tight serving loops, harnesses that forbid it.)  The megakernel's scratch -- the ray
+// counters, the two per-tile cost buffers, the tile order made from them and the bucket counts of tile_order.cu, which
+// the other entry points allocate per scene and grow on demand -- lives in ONE file-scope device array of fixed size;
+// every GPU that loads the library holds it (3.1 MB) until the process exits.  In host code the array's name is only a
+// stand-in for the symbol: its device address is asked for once per device (cudaGetSymbolAddress with that device
+// current) and that pointer is what the kernels are given.
+#define RTC_STATIC_MAX_TILES (1u << 18)  // 8x4-pixel tiles: 8,388,608 pixels; 3840x2160 (259,200 tiles) fits
+namespace {
+struct StaticScratch {
+    unsigned long long counters[8];                              // RenderParams::counters
+    unsigned cost[2][RTC_STATIC_MAX_TILES + 2];                  // tile costs + the 64-bit sum, two buffers taking turns
+    unsigned order[RTC_STATIC_MAX_TILES];                        // RenderParams::tile_order
+    unsigned buckets[4 * (RTC_STATIC_MAX_TILES / 1024 + 1) + 3];  // tile_order.cu: bucket counts + heavy-tile counts
+};
+}  // namespace
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+namespace {
+constexpr int kStaticDevices = 64;
+// What the array of a device holds from the calls before (it is shared by every call on that device, whatever the scene).
+struct StaticState {
+    StaticScratch* ptr = nullptr;  // device address of g_static_scratch on this device
+    const rtc_scene* scene = nullptr;
+    rtc_scene::View pending_view{}, order_view{};
+    size_t pending = 0, order_tiles = 0;  // as rtc_scene::pending / order_tiles
+    int parity = 0;
+};
+StaticState g_static[kStaticDevices];
+}  // namespace
+
+// Set-up, once per device (the device must be current).  No allocation: the array came with the module.
+static int static_scratch_setup(int device, StaticState** out) {
+    if (device < 0 || device >= kStaticDevices) return fail(RTC_ERR_INVALID, "rtc_render_device_static: device index out of range");
+    StaticState& st = g_static[device];
+    if (!st.ptr) {
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) return fail(RTC_ERR_CUDA, "rtc_render_device_static: bad address of the static scratch array");
+        CUDA_TRY(cudaMemset(p, 0, sizeof(StaticScratch)));  // (zero at module load already; the cost buffers MUST start at zero)
+        st.ptr = static_cast<StaticScratch*>(p);
+    }
+    *out = &st;
+    return RTC_OK;
+}
+
+extern "C" {
+
+uint64_t rtc_static_max_tiles(void) { return RTC_STATIC_MAX_TILES; }
+
+int rtc_render_device_static(rtc_scene* s, const rtc_camera* cam, int max_depth, double* d_rgb, void* stream_, rtc_stats* stats) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!s || !cam || !d_rgb) return fail(RTC_ERR_INVALID, "rtc_render_device_static: NULL scene, camera or frame");
+    if (max_depth < 0 || max_depth > 7) return fail(RTC_ERR_INVALID, "render: max_depth must be in [0,7]");
+    if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID, "render: empty frame");
+    const size_t n_tiles = frame_tiles(cam->hsize, cam->vsize);
+    if (cam->hsize > (1ull << 24) || cam->vsize > (1ull << 24) || n_tiles > RTC_STATIC_MAX_TILES) {
+        char buf[200];
+        std::snprintf(buf, sizeof buf,
+                      "rtc_render_device_static: a %llux%llu frame is %zu tiles of %ux%u pixels, the static scratch holds %u "
+                      "(use rtc_render_device)",
+                      (unsigned long long)cam->hsize, (unsigned long long)cam->vsize, n_tiles, RTC_TILE_W, RTC_TILE_H, RTC_STATIC_MAX_TILES);
+        return fail(RTC_ERR_INVALID, buf);
+    }
+    CUDA_TRY(cudaSetDevice(s->device));
+    StaticState* st = nullptr;
+    if (int rc = static_scratch_setup(s->device, &st)) return rc;
+    StaticScratch* sc = st->ptr;
+    const bool same_scene = st->scene == s;
+    if (!same_scene) {  // another scene: the costs and the order at hand say nothing about this one
+        st->scene = s;
+        st->order_tiles = 0;
+    }
+
+    RenderParams P{};
+    P.cam.hsize = cam->hsize;
+    P.cam.vsize = cam->vsize;
+    P.cam.half_width = cam->half_width;
+    P.cam.half_height = cam->half_height;
+    P.cam.pixel_size = cam->pixel_size;
+    std::memcpy(P.cam.inv, cam->inverse, sizeof P.cam.inv);
+    P.max_depth = max_depth;
+    P.tile_rows = 1, P.part = 0, P.n_parts = 1;  // the whole frame
+    P.rows = cam->vsize;
+    P.tiles_x = (unsigned)((cam->hsize + RTC_TILE_W - 1) / RTC_TILE_W);
+    const unsigned n_tile_rows = (unsigned)((P.rows + RTC_TILE_H - 1) / RTC_TILE_H);
+    P.n_items = (unsigned long long)n_tiles * 32ull;
+    P.deal_n = 1;
+    P.row_group = 4;  // tile rows top to bottom (only read while there is no order yet)
+    P.n_row_groups = n_tile_rows / P.row_group;
+    P.row_stride = 1;
+    P.scale = s->wf_scale;
+    P.out = d_rgb;
+    P.counters = sc->counters;
+
+    // the same protocol as enqueue_frame: last call's costs -> this call's order; a view rendered in the order made
+    // from its own costs records nothing
+    rtc_scene::View view{};
+    view.cam = *cam;
+    view.depth = max_depth;
+    view.tile_rows = 1, view.part = 0, view.n_parts = 1, view.deal_rank = 0, view.deal_n = 1;
+    view.last_bucket = 3;
+    const size_t words = cost_words(n_tiles);
+    unsigned* prev = sc->cost[st->parity ^ 1];
+    bool order_made = false;
+    CUDA_TRY(cudaMemsetAsync(sc->counters, 0, sizeof sc->counters, stream));
+    const bool timed = stats != nullptr;
+    if (timed) CUDA_TRY(cudaEventRecord(s->ev0, stream));
+    if (same_scene && st->pending == n_tiles) {
+        CUDA_TRY((cudaError_t)launch_tile_order(prev, reinterpret_cast<const unsigned long long*>(prev + words - 2), sc->buckets, sc->order,
+                                                (unsigned)n_tiles, 3, stream));
+        st->order_tiles = n_tiles;
+        st->order_view = st->pending_view;
+        order_made = true;
+    }
+    if (st->pending) CUDA_TRY(cudaMemsetAsync(prev, 0, cost_words(st->pending) * sizeof(unsigned), stream));  // clean for its next turn
+    st->pending = 0;
+    P.tile_order = st->order_tiles == n_tiles ? sc->order : nullptr;
+    P.heavy_tiles = sc->buckets + 4 * ((n_tiles + 1023) / 1024);
+    if (!(P.tile_order && std::memcmp(&st->order_view, &view, sizeof view) == 0)) {
+        P.cost_peer[0] = sc->cost[st->parity];
+        P.cost_tiles = (unsigned)(words - 2);
+        st->parity ^= 1;
+        st->pending = n_tiles;
+        st->pending_view = view;
+    }
+    CUDA_TRY((cudaError_t)launch_mega(s, P, 1, stream));
+    if (!timed) return RTC_OK;  // enqueued only: nothing is synchronised, capacity errors are not reported
+
+    CUDA_TRY(cudaEventRecord(s->ev1, stream));
+    unsigned long long c[8];
+    CUDA_TRY(cudaMemcpyAsync(c, sc->counters, sizeof c, cudaMemcpyDeviceToHost, stream));
+    CUDA_TRY(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    *stats = rtc_stats{};
+    stats->primary_rays = c[1];
+    stats->shadow_rays = c[2];
+    stats->secondary_rays = c[3];
+    stats->shadow_rays_culled = c[5];
+    stats->pixels = cam->hsize * cam->vsize;
+    stats->kernel_ms = ms;
+    stats->launches = order_made ? 3 : 1;
+    if (c[4]) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "render: per-ray capacity exceeded (bits %llu, see rtc_render)", c[4]);
+        return fail(RTC_ERR_CAPACITY, buf);
+    }
+    return RTC_OK;
+}
+
+}  // extern "C"
