@@ -168,14 +168,28 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     // deepest pixels of a small partition -- glass boxes, 6 levels -- is what its frame time is made of.
     constexpr int HL = RTC_HEAVY_LANES;
     constexpr bool PIPE = MIXED && HL == 8;
+    // RTC_HEAVY_GROUPS = G > 1: G such groups of four lanes per pixel, HT = 4 G lanes in all, which split the pixel's RAY
+    // TREE between them.  Every group starts at the primary ray; at the first hit that spawns BOTH a reflected and a
+    // refracted ray the groups whose next path bit is 0 follow the reflection and the others the refraction, and so on
+    // until the log2(G) bits are used up -- from there a group walks its subtree with its own ray stack as before.  A hit
+    // on the shared upper part of the tree is traced by several groups but SHADED (shadow rays, lighting, ray counts) by
+    // exactly one, the group whose remaining path bits are all 0; the partial sums of all HT lanes are added as integers
+    // at the end, so the pixel is bit-identical.  The chain of dependent trips behind a glass pixel (63 hits at depth 5)
+    // becomes log2(G) + 63 / G hits.
+    constexpr int HG = MIXED ? RTC_HEAVY_GROUPS : 1;
+    constexpr int HT = HL * HG;
+    constexpr bool SPLIT = HG > 1;
+    static_assert(HG == 1 || HG == 2 || HG == 4 || HG == 8, "RTC_HEAVY_GROUPS: 1, 2, 4 or 8");
+    static_assert(!SPLIT || HL == 4, "groups split the tree of a pixel only in the four-lane mode");
+    constexpr int HG_BITS = HG == 8 ? 3 : HG == 4 ? 2 : HG == 2 ? 1 : 0;
     // (of the heavy tiles at the head of the order this renderer is dealt its runs, like of all others)
     unsigned long long heavy_items = 0ull;
     if (MIXED && P.tile_order) {
         const unsigned h = __ldg(P.heavy_tiles), run = 1u << P.deal_shift, round = run * P.deal_n;
         const unsigned rem = h % round, lo = P.deal_rank * run;
-        heavy_items = (unsigned long long)(h / round * run + (rem > lo ? min(rem - lo, run) : 0u)) * (32ull * HL);
+        heavy_items = (unsigned long long)(h / round * run + (rem > lo ? min(rem - lo, run) : 0u)) * (32ull * HT);
     }
-    const unsigned long long n_items = P.n_items + heavy_items / HL * (HL - 1);  // a heavy tile is 32 x HL lane items instead of 32
+    const unsigned long long n_items = P.n_items + heavy_items / HT * (HT - 1);  // a heavy tile is 32 x HT lane items instead of 32
     int lpp = MIXED ? 1 : LPP;  // lanes per pixel of the tile this warp is working on
     extern __shared__ double s_mem[];  // PK_SLOTS x RTC_BLOCK doubles, then (MESH) S.stack_cap x RTC_BLOCK ints
     double* pk = s_mem + threadIdx.x;
@@ -184,6 +198,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
     const unsigned lt_mask = (1u << lane) - 1u;
     unsigned sub = MIXED ? 0u : lane & (unsigned)(LPP - 1);  // which of the pixel's lanes this is
     bool wpend = false;                                // LPP > 1: the pixel is through, its sum not yet written
+    unsigned gid = 0, grp = 0;  // SPLIT: the lane's group among the pixel's; the bits of it not used for a branch yet
+    int nb = 0;                 // ... and how many of them are left
+    (void)gid, (void)grp, (void)nb;
 
     int state = ST_IDLE;
     bool done = false;
@@ -215,12 +232,12 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 long long a0 = __double_as_longlong(PK(PK_PCOL)), a1 = __double_as_longlong(PK(PK_PCOL + 1)),
                           a2 = __double_as_longlong(PK(PK_PCOL + 2));
 #pragma unroll
-                for (int sft = 1; sft < (MIXED ? HL : LPP); sft <<= 1) {
+                for (int sft = 1; sft < (MIXED ? HT : LPP); sft <<= 1) {
                     a0 += __shfl_xor_sync(0xffffffffu, a0, sft);
                     a1 += __shfl_xor_sync(0xffffffffu, a1, sft);
                     a2 += __shfl_xor_sync(0xffffffffu, a2, sft);
                 }
-                if (wpend && sub == 0) {
+                if (wpend && sub == 0 && gid == 0) {
                     const double inv_scale = 1.0 / P.scale;  // a power of two: exact
                     V3 pcol = v3((double)a0 * inv_scale, (double)a1 * inv_scale, (double)a2 * inv_scale);
                     if (P.out8) {
@@ -281,7 +298,11 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         const bool heavy = item < heavy_items;  // the same for the whole warp: heavy_items % 32 == 0
                         lpp = heavy ? HL : 1;
                         sub = heavy ? (unsigned)item & (unsigned)(HL - 1) : 0u;
-                        pitem = heavy ? item / (unsigned)HL : item - heavy_items / HL * (HL - 1);
+                        pitem = heavy ? item / (unsigned)HT : item - heavy_items / HT * (HT - 1);
+                        if constexpr (SPLIT) {
+                            gid = grp = heavy ? ((unsigned)item / (unsigned)HL) & (unsigned)(HG - 1) : 0u;
+                            nb = heavy ? HG_BITS : 0;
+                        }
                     } else {
                         pitem = item / (unsigned)LPP;
                     }
@@ -322,7 +343,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                         rsp = 0;
                         state = ST_CLOSEST;
                         if (PIPE && sub != 0) state = ST_WAIT;  // (lpp == HL: only there sub != 0) a shadow lane: waits for lane 0's hits
-                        if (sub == 0) n_primary++;
+                        if (sub == 0 && gid == 0) n_primary++;
                     }
                     // items outside the frame are simply dropped: the lane asks again next trip
                 }
@@ -444,8 +465,9 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 // transparency (world.zig:101-102, :178)
                 // ... and when every material of the scene has refractive index 1.0 (dragons.json's glass boxes),
                 // n1 = n2 = 1.0 whatever the containers list holds (world.zig:236-254): the walk is skipped.
+                // (SPLIT: a group that is not the one shading this hit goes straight on to the children)
                 if (M.transparency != 0.0 && !S.ri_all_one) state = ST_CONTAINERS;
-                else state = S.n_lights > (int)sub ? ST_SHADOW : -1;  // no lights (left for this lane): straight to the children below
+                else state = S.n_lights > (int)sub && !(SPLIT && grp != 0) ? ST_SHADOW : -1;  // no lights (left for this lane): straight to the children below
                 if (PIPE && lpp == HL) {  // lane 0 of a pipelined pixel: its shadow rays are the other lanes' business
                     publish = S.n_lights > 0;
                     if (state == ST_SHADOW) state = -1;
@@ -462,7 +484,7 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 PK(PK_N1) = ri_c;
                 PK(PK_N2) = ri_hit;
             }
-            state = S.n_lights > (int)sub ? ST_SHADOW : -1;
+            state = S.n_lights > (int)sub && !(SPLIT && grp != 0) ? ST_SHADOW : -1;
             if (PIPE && lpp == HL) state = -1;
         } else if (state == ST_SHADOW) {
             // Material.lighting (material.zig:40-74)
@@ -581,22 +603,32 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 refl_w *= reflectance;
                 refr_w *= (1.0 - reflectance);
             }
+            bool take_refr = spawn_refr, take_refl = spawn_refl, count = sub == 0;
+            if constexpr (SPLIT) {
+                count = count && grp == 0;  // the group that shades this hit counts its children
+                if (nb > 0 && spawn_refr && spawn_refl) {  // the tree branches: the groups on this hit part here
+                    if (grp & 1u) take_refl = false;
+                    else take_refr = false;
+                    grp >>= 1;
+                    nb--;
+                }
+            }
             if (spawn_refr || spawn_refl) {
                 V3 h_point = ro + rd * PK(PK_T);  // world.zig:219
                 if (spawn_refr) {
                     V3 under = h_point - h_normal * 1e-5;
-                    if (rsp < RTC_RAY_STACK) {
+                    if (take_refr && rsp < RTC_RAY_STACK) {
                         rays[rsp++] = {under.x, under.y, under.z, refr_dir.x, refr_dir.y, refr_dir.z, rw * refr_w, remaining - 1, 0};
                     }
-                    if (sub == 0) n_secondary++;
+                    if (count) n_secondary++;
                 }
                 if (spawn_refl) {
                     V3 h_over = h_point + h_normal * 1e-5;
                     V3 reflectv = rd - h_normal * (2.0 * dot(rd, h_normal));
-                    if (rsp < RTC_RAY_STACK) {
+                    if (take_refl && rsp < RTC_RAY_STACK) {
                         rays[rsp++] = {h_over.x, h_over.y, h_over.z, reflectv.x, reflectv.y, reflectv.z, rw * refl_w, remaining - 1, 0};
                     }
-                    if (sub == 0) n_secondary++;
+                    if (count) n_secondary++;
                 }
             }
             pop_next = true;

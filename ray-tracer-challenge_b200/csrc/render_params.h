@@ -27,6 +27,10 @@ namespace rtc {
 #ifndef RTC_HEAVY_LANES
 #define RTC_HEAVY_LANES 4
 #endif
+// groups of RTC_HEAVY_LANES lanes per pixel on the heavy tiles, which split the pixel's ray tree (render_kernel.cuh SPLIT)
+#ifndef RTC_HEAVY_GROUPS
+#define RTC_HEAVY_GROUPS 1
+#endif
 #define RTC_FEAT_CSG 1       // render_kernel<MESH, LPP, FEAT>: see render_kernel.cuh
 #define RTC_FEAT_PATTERNS 2
 #define RTC_MAX_SHARE 8    // renderers (GPUs) that can share one frame tile by tile (RenderParams::cost_peer)
