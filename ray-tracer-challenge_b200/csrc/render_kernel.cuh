@@ -275,9 +275,13 @@ __global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MI
                 }
                 if (LPP == 1 && P.copy_out) {  // for the copy warps (copy_finished_rows): one more tile of its row is done
                     const unsigned row = (unsigned)PK(PK_SPARE + 2) / P.tiles_x;
-                    __threadfence();  // the tile's pixels before the count
-                    if (atomicAdd(P.row_count + row, 1u) + 2u == P.tiles_x) {  // (counts start at 0xffffffff) the row's last tile
-                        __threadfence();
+                    // the tile's pixels before the count: a RELEASE on the counter, not __threadfence() -- that one compiles to
+                    // MEMBAR.SC + CCTL.IVALL, and dropping the SM's whole L1 (the BVH nodes) after every tile cost 15-20 % of the
+                    // kernel (measured; profiles/README.md).  The one thread per row that goes on to announce it fences fully.
+                    unsigned before;
+                    asm volatile("atom.release.gpu.global.add.u32 %0, [%1], 1;" : "=r"(before) : "l"(P.row_count + row) : "memory");
+                    if (before + 2u == P.tiles_x) {  // (counts start at 0xffffffff) the row's last tile
+                        __threadfence_system();  // (the list may be in host memory, read by the host: rtc_api.cu render_to_pinned)
                         P.done_list[atomicAdd(P.copy_ctl, 1u) + 1u] = row;
                     }
                 }

@@ -165,6 +165,11 @@ int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 // tile_order.cu: order[] = the tiles 0..n_tiles-1, stably sorted into four cost buckets (most expensive first)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
                       int last_bucket, cudaStream_t stream);
+// ... or for frames streamed to a host canvas: bands of rows, cheapest band first, every tile started ahead of its row by what it costs
+size_t row_order_temp_bytes(unsigned n_tiles);
+size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x);
+int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned n_tiles, unsigned tiles_x,
+                     unsigned band_rows, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream);
 
 // render_inst_*.cu: the instantiations of render_kernel<MESH, LPP, FEAT>, one translation unit per (MESH, FEAT).
 // smem = dynamic shared memory per CTA (parked state + the BVH traversal stacks).

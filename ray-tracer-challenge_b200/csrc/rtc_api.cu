@@ -91,6 +91,8 @@ struct rtc_scene {
     unsigned* d_cost_own[2] = {nullptr, nullptr};  // own allocations (unused when the caller provided shared buffers)
     unsigned* d_scratch = nullptr;                 // bucket counts of tile_order.cu + the heavy-tile count
     unsigned* d_tile_order = nullptr;
+    unsigned* d_row_work = nullptr;  // tile_order.cu launch_row_order: keys, sorted keys, tile numbers; then cub's temporary storage
+    size_t row_work_cap = 0, row_temp_bytes = 0;
     size_t tile_cap = 0;        // tiles the own cost buffers hold
     size_t order_cap = 0;       // tiles d_scratch / d_tile_order hold
     // A frame records costs only when the order at hand was not made from this very view (camera, depth, partition): a
@@ -110,6 +112,14 @@ struct rtc_scene {
     unsigned* d_done = nullptr;  // RenderParams::done_list + copy_ctl (decoupled host canvases)
     size_t done_cap = 0;
     bool last_copied = false;    // the last frame's copy warps delivered it to the host canvas
+    // ... or the HOST moves them: the kernel announces every finished row of tiles in h_done (pinned, mapped) and the
+    // calling thread hands runs of finished rows to the copy engine on copy_stream while the kernel renders the rest
+    unsigned* h_done = nullptr;      // host address
+    unsigned* h_done_dev = nullptr;  // the same memory as the device addresses it
+    size_t h_done_cap = 0;
+    static constexpr int kCopyStreams = 4;
+    cudaStream_t copy_stream[kCopyStreams] = {};  // runs of rows go to them in turn: the set-up of one copy hides behind the bytes of another
+    bool last_announced = false;  // the last frame announced its rows in h_done
     struct Share {
         unsigned rank = 0, n = 1;
         unsigned* cost[2][RTC_MAX_SHARE] = {};  // [buffer][renderer], as THIS device addresses them
@@ -254,6 +264,10 @@ void rtc_scene_destroy(rtc_scene* s) {
         if (s->d_cost_own[i]) cudaFree(s->d_cost_own[i]);
     if (s->d_scratch) cudaFree(s->d_scratch);
     if (s->d_done) cudaFree(s->d_done);
+    if (s->d_row_work) cudaFree(s->d_row_work);
+    if (s->h_done) cudaFreeHost(s->h_done);
+    for (cudaStream_t cs : s->copy_stream)
+        if (cs) cudaStreamDestroy(cs);
     if (s->d_tile_order) cudaFree(s->d_tile_order);
     for (int i = 0; i < 2; i++) {
         if (s->wf_rays[i]) cudaFree(s->wf_rays[i]);
@@ -614,6 +628,7 @@ struct Target {              // where a frame goes
     bool full_frame = false; // rows of the partition at their frame positions (else packed)
     bool spread_rows = false;  // canvas in mapped host memory: strided row order, no cost order (see enqueue_frame)
     double* copy_out = nullptr;  // mapped host canvas the frame in `rgb` (device memory) is moved to BY THE KERNEL's copy warps
+    bool announce = false;       // the frame in `rgb` / `rgba` (device memory) is moved by the HOST: finished rows of tiles are announced in h_done
 };
 
 // Makes the statistics of the frame in ring slot `slot` (waits for it if it is still on the stream).
@@ -668,7 +683,7 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     if (part->n_parts == 0 || part->part >= part->n_parts || part->tile_rows == 0)
         return fail(RTC_ERR_INVALID, "render: bad partition");
     CUDA_TRY(cudaSetDevice(s->device));
-    s->last_copied = false;
+    s->last_copied = s->last_announced = false;
     // a free ring slot: the oldest frame nobody fetched is resolved (its time still counts for the kernel choice) and dropped
     if (s->seq_next - s->seq_pop == (uint64_t)rtc_scene::kRing) {
         const int old = (int)(s->seq_pop % rtc_scene::kRing);
@@ -736,7 +751,11 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             const char* e = std::getenv("RTC_COPY_SPREAD");
             return !(e && e[0] == '0');
         }();
-        if (forced >= 0 ? forced != 1 : (tg.spread_rows || (tg.copy_out && copy_spread))) {
+        static const bool dma_spread = [] {  // rows announced to the host: measured both ways (profiles/README.md)
+            const char* e = std::getenv("RTC_DMA_SPREAD");
+            return e && e[0] == '1';
+        }();
+        if (forced >= 0 ? forced != 1 : (tg.spread_rows || (tg.copy_out && copy_spread) || (tg.announce && dma_spread))) {
             st = forced > 1 ? (unsigned)forced : (unsigned)(0.381966 * P.n_row_groups);
             auto gcd = [](unsigned a, unsigned b) {
                 while (b) {
@@ -836,8 +855,9 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         int v = e ? std::atoi(e) : 4;  // measured on B200, dragons 1080p e2e ms per frame: 4 CTAs 1.27, 8: 1.28, 16: 1.29 (direct stores: 1.54)
         return (unsigned)(v >= 0 && v <= 64 ? v : 4);
     }();
-    if (tg.copy_out && tg.rgb && tg.full_frame && !dealt && (P.n_parts == 1 || P.tile_rows % RTC_TILE_H == 0) && lpp == 1 && copy_ctas > 0 &&
-        (int)copy_ctas * 2 <= s->grid) {
+    const bool by_warps = tg.copy_out && tg.rgb && copy_ctas > 0 && (int)copy_ctas * 2 <= s->grid;
+    const bool by_host = tg.announce && (tg.rgb || tg.rgba);
+    if ((by_warps || by_host) && tg.full_frame && !dealt && (P.n_parts == 1 || P.tile_rows % RTC_TILE_H == 0) && lpp == 1) {
         // per row of tiles: a counter of finished tiles; the list of finished rows; the two cursors -- all set to 0xffffffff
         const size_t n_rows = n_tile_rows, words = 2 * n_rows + 2;
         if (s->done_cap < words) {
@@ -849,13 +869,33 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             s->done_cap = words;
         }
         CUDA_TRY(cudaMemsetAsync(s->d_done, 0xff, words * sizeof(unsigned), stream));
-        P.copy_out = tg.copy_out;
         P.done_list = s->d_done;
         P.copy_ctl = s->d_done + n_rows;
         P.row_count = s->d_done + n_rows + 2;
-        P.copy_ctas = copy_ctas;
         P.copy_rows = (unsigned)n_rows;
-        s->last_copied = true;
+        if (by_host) {
+            if (s->h_done_cap < n_rows) {
+                CUDA_TRY(cudaStreamSynchronize(stream));
+                if (s->h_done) cudaFreeHost(s->h_done);
+                s->h_done = s->h_done_dev = nullptr;
+                s->h_done_cap = 0;
+                CUDA_TRY(cudaHostAlloc(&s->h_done, n_rows * sizeof(unsigned), cudaHostAllocMapped));
+                CUDA_TRY(cudaHostGetDevicePointer(&s->h_done_dev, s->h_done, 0));
+                s->h_done_cap = n_rows;
+            }
+            for (cudaStream_t& cs : s->copy_stream)
+                if (!cs) CUDA_TRY(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+            // (the frame before this one was collected by the caller before it came back: nobody reads the list any more)
+            std::memset(s->h_done, 0xff, n_rows * sizeof(unsigned));
+            P.copy_out = tg.rgb ? tg.rgb : reinterpret_cast<double*>(tg.rgba);  // (here it only says: count the finished rows)
+            P.done_list = s->h_done_dev;
+            P.copy_ctas = 0;  // no copy warps
+            s->last_announced = true;
+        } else {
+            P.copy_out = tg.copy_out;
+            P.copy_ctas = copy_ctas;
+            s->last_copied = true;
+        }
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, 8 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventRecord(s->rev0[slot], stream));
@@ -899,13 +939,53 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         // buckets 1.62 (the cheap 85 % of the bytes all come at the end), plain order 1.25, >= 8x first 1.21; the expensive
         // buckets interleaved evenly with the cheap tiles 1.21 -- and skybox.json 4K 9.6 instead of 2.3: writes that
         // jump about the host canvas are slow, writes that walk through it are not (profiles/README.md).
+        // < 0: bands of -last_bucket rows of tiles, cheapest band first, every tile started ahead of its row by what it
+        // costs (tile_order.cu launch_row_order).  A band is what one copy moves: ~1.5 MB (a copy is set up in 3.5 us), or the
+        // block of rows a partition holds together in the frame.  RTC_COPY_BUCKETS >= 0 keeps the bucket orders.
         static const int copy_buckets = [] {
             const char* e = std::getenv("RTC_COPY_BUCKETS");
-            int v = e ? std::atoi(e) : 1;
-            return v >= 0 && v <= 3 ? v : 1;
+            int v = e ? std::atoi(e) : -1;
+            return v >= -1 && v <= 3 ? v : -1;
         }();
-        view.last_bucket = tg.copy_out ? copy_buckets : 3;
-        if (s->pending == n_tiles) {
+        view.last_bucket = 3;
+        if (tg.copy_out || tg.announce) {
+            view.last_bucket = copy_buckets;
+            if (copy_buckets < 0) {
+                static const long band_kb = [] {
+                    const char* e = std::getenv("RTC_BAND_KB");
+                    long v = e ? std::atol(e) : 1536;
+                    return v > 0 ? v : 1536;
+                }();
+                const size_t tile_row_bytes = (size_t)cam->hsize * RTC_TILE_H * (tg.rgba ? 4 : 24);
+                size_t band = std::max<size_t>(1, ((size_t)band_kb << 10) / tile_row_bytes);
+                if (P.n_parts > 1) band = std::max<size_t>(1, P.tile_rows / RTC_TILE_H);
+                view.last_bucket = -(int)std::min<size_t>(band, 4096);
+            }
+        }
+        if (s->pending == n_tiles && s->pending_view.last_bucket < 0) {
+            if (s->row_work_cap < n_tiles) {
+                CUDA_TRY(cudaStreamSynchronize(stream));
+                if (s->d_row_work) cudaFree(s->d_row_work);
+                s->d_row_work = nullptr;
+                s->row_work_cap = 0;
+                s->row_temp_bytes = row_order_temp_bytes((unsigned)n_tiles);
+                CUDA_TRY(cudaMalloc(&s->d_row_work, (3 * n_tiles + 3 * (n_tiles + 8) + 8) * sizeof(unsigned) + 256 + s->row_temp_bytes));  // (rows <= tiles)
+                s->row_work_cap = n_tiles;
+            }
+            static const unsigned lead_pct = [] {  // how far ahead, in per cent of the estimate (warps of the grid working side by side)
+                const char* e = std::getenv("RTC_ROW_LEAD");
+                int v = e ? std::atoi(e) : 100;
+                return (unsigned)(v >= 0 && v <= 1000 ? v : 100);
+            }();
+            const unsigned lead = (unsigned)((unsigned long long)s->grid * (RTC_BLOCK_THREADS / 32) * lead_pct / 100u);
+            void* temp = reinterpret_cast<char*>(s->d_row_work) + (((3 * s->row_work_cap + 3 * (s->row_work_cap + 8) + 8) * sizeof(unsigned) + 255) & ~size_t(255));
+            CUDA_TRY((cudaError_t)launch_row_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
+                                                   s->d_row_work, s->d_tile_order, (unsigned)n_tiles, P.tiles_x, (unsigned)-s->pending_view.last_bucket, lead,
+                                                   temp, s->row_temp_bytes, stream));
+            s->order_tiles = n_tiles;
+            s->order_view = s->pending_view;
+            F.order_made = true;
+        } else if (s->pending == n_tiles) {
             // the previous frame's costs (complete in EVERY renderer's copy: a shared frame ends with a barrier) -> the order
             CUDA_TRY((cudaError_t)launch_tile_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
                                                     s->d_scratch, s->d_tile_order, (unsigned)n_tiles, s->pending_view.last_bucket, stream));
@@ -1176,6 +1256,165 @@ static int copy_partition_in_place(const rtc_camera* cam, const rtc_partition* p
     return RTC_OK;
 }
 
+// A frame (or row partition) for a canvas in PINNED host memory, moved by the copy engine while it renders: the kernel
+// renders into the scene's frame-sized device buffer at full speed (cost order, no store crosses PCIe) and announces every
+// finished row of tiles -- RTC_TILE_H scanlines, contiguous in the frame -- in a list in mapped host memory; this thread,
+// which would only wait for the frame anyway, polls the list and hands runs of neighbouring finished rows to
+// cudaMemcpyAsync on a stream of its own.  The link works at DMA speed (57 GB/s measured against 50-52 for SM-written host
+// memory) from the first finished rows on and no CTA is given up for copying.  px_bytes: 24 (f64 RGB) or 4 (RGBA8).
+static int render_to_pinned(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_partition* part, void* h_dst, size_t px_bytes,
+                            rtc_stats* stats) {
+    if (stats) std::memset(stats, 0, sizeof *stats);
+    const bool whole = !part || part->n_parts <= 1;
+    const size_t row_bytes = (size_t)cam->hsize * px_bytes, frame_bytes = row_bytes * cam->vsize;
+    int rc = ensure_frame(s, frame_bytes + 16);
+    if (rc) return rc;
+    Target tg;
+    if (px_bytes == 4) tg.rgba = reinterpret_cast<unsigned char*>(s->d_frame);
+    else tg.rgb = s->d_frame;
+    tg.full_frame = true;
+    tg.announce = true;
+    int slot = -1;
+    rc = enqueue_frame(s, cam, max_depth, part, tg, 0, false, &slot, false);
+    if (rc && rc != RTC_ERR_CAPACITY) return rc;
+    auto collect = [&](int rc0) {
+        while (s->seq_next - s->seq_pop > 1) pop_frame(s, nullptr);
+        const int rp = pop_frame(s, stats);
+        return rc0 ? rc0 : rp;
+    };
+    if (!s->last_announced) {  // rendered another way (wavefront, several lanes per pixel, an empty partition): copied afterwards
+        rc = collect(rc);
+        if (rc) return rc;
+        if (whole) {
+            CUDA_TRY(cudaMemcpy(h_dst, s->d_frame, frame_bytes, cudaMemcpyDeviceToHost));
+            return RTC_OK;
+        }
+        return copy_partition_in_place(cam, part, s->d_frame, h_dst, px_bytes);
+    }
+    const rtc_partition whole_part = {1, 0, 1};
+    const rtc_partition& pt = part ? *part : whole_part;
+    const uint64_t rows = rtc_partition_rows(cam->vsize, &pt);
+    const unsigned n_rows = (unsigned)((rows + RTC_TILE_H - 1) / RTC_TILE_H);
+    // scanlines [y0, y1) of the frame that row r of tiles of the partition covers (render_kernel.cuh copy_finished_rows)
+    auto span = [&](unsigned r, uint64_t& y0, uint64_t& y1) {
+        const uint64_t pr0 = (uint64_t)r * RTC_TILE_H, pr1 = std::min<uint64_t>(pr0 + RTC_TILE_H, rows);
+        y0 = ((pr0 / pt.tile_rows) * pt.n_parts + pt.part) * pt.tile_rows + pr0 % pt.tile_rows;
+        y1 = y0 + (pr1 - pr0);
+    };
+    // A copy is set up in ~3.5 us whatever its size (measured: 49.8 MB in 1 MB pieces 47 GB/s, in 4 MB pieces 54, in one
+    // piece 56.4; two streams change nothing), so pieces should be as large as the link allows without waiting for them:
+    // a stream takes a new run of finished rows only when its last copy is through, and then the whole run that has
+    // gathered meanwhile.  While the link keeps up the pieces stay small and early; when it falls behind they grow.
+    static const size_t min_run = [] {  // bytes below which a run that can still grow is not worth a copy of its own
+        const char* e = std::getenv("RTC_DMA_MIN_KB");
+        long v = e ? std::atol(e) : 1024;
+        return (size_t)(v > 0 ? v : 1) << 10;
+    }();
+    static const int n_streams = [] {
+        const char* e = std::getenv("RTC_DMA_STREAMS");
+        int v = e ? std::atoi(e) : 2;
+        return v >= 1 && v <= rtc_scene::kCopyStreams ? v : 2;
+    }();
+    static const bool trace = std::getenv("RTC_DMA_TRACE") != nullptr;  // timeline of one frame on stderr
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto now_us = [&] { return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_begin).count(); };
+    std::vector<double> t_row;                      // when row k of the list was seen
+    std::vector<std::pair<double, double>> t_copy;  // when a copy was handed over, its megabytes
+    bool busy[rtc_scene::kCopyStreams] = {};
+    std::vector<unsigned char> st(n_rows, 0);  // 0 rendering, 1 finished, 2 handed to the copy engine
+    volatile unsigned* list = s->h_done;
+    unsigned taken = 0, copied = 0, first_open = 0;  // first_open: no row below it is still waiting for a copy
+    bool frame_over = false;
+    int cerr = RTC_OK;
+    unsigned idle = 0;
+    while (copied < n_rows && cerr == RTC_OK) {
+        bool news = false;
+        while (taken < n_rows) {
+            const unsigned r = list[taken];
+            if (r == 0xffffffffu) break;
+            if (r < n_rows) st[r] = 1;
+            taken++;
+            news = true;
+            if (trace) t_row.push_back(now_us());
+        }
+        if (news) std::atomic_thread_fence(std::memory_order_acquire);
+        if (!news && !frame_over && taken < n_rows && (++idle & 63u) == 0) {  // now and then: is the frame over, or broken?
+            cudaError_t q = cudaEventQuery(s->rev2[slot]);
+            if (q == cudaSuccess) {
+                frame_over = true;
+                continue;  // (read the list once more: everything the kernel announced is there now)
+            }
+            if (q != cudaErrorNotReady) cerr = fail(RTC_ERR_CUDA, std::string("render: ") + cudaGetErrorString(q));
+        }
+        if (frame_over && !news && taken < n_rows) {  // the kernel ended without announcing every row: its error bits say why
+            for (unsigned k = 0; k < n_rows; k++)
+                if (st[k] == 0) st[k] = 1;  // whatever is there goes out; the frame's status below is what counts
+            taken = n_rows;
+        }
+        const bool all_in = taken == n_rows;
+        for (int k = 0; k < n_streams && copied < n_rows && cerr == RTC_OK; k++) {
+            if (busy[k]) {
+                cudaError_t q = cudaStreamQuery(s->copy_stream[k]);
+                if (q == cudaErrorNotReady) continue;
+                if (q != cudaSuccess) {
+                    cerr = fail(RTC_ERR_CUDA, std::string("copy stream: ") + cudaGetErrorString(q));
+                    break;
+                }
+                busy[k] = false;
+            }
+            while (first_open < n_rows && st[first_open] == 2) first_open++;
+            for (unsigned a = first_open; a < n_rows;) {
+                if (st[a] != 1) {
+                    a++;
+                    continue;
+                }
+                // the run of finished rows starting here that is also one run of bytes in the frame
+                uint64_t y0, y1;
+                span(a, y0, y1);
+                unsigned b = a + 1;
+                for (; b < n_rows && st[b] == 1; b++) {
+                    uint64_t z0, z1;
+                    span(b, z0, z1);
+                    if (z0 != y1) break;
+                    y1 = z1;
+                }
+                // taken when large enough, when it cannot grow any more, or when the frame is through
+                const bool closed = (a == 0 || st[a - 1] == 2) && (b == n_rows || st[b] == 2);
+                if ((y1 - y0) * row_bytes >= min_run || closed || all_in || !whole) {
+                    cudaError_t e = cudaMemcpyAsync((char*)h_dst + y0 * row_bytes, (const char*)s->d_frame + y0 * row_bytes, (y1 - y0) * row_bytes,
+                                                    cudaMemcpyDeviceToHost, s->copy_stream[k]);
+                    if (e != cudaSuccess) {
+                        cerr = fail(RTC_ERR_CUDA, std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e));
+                        break;
+                    }
+                    for (unsigned j = a; j < b; j++) st[j] = 2;
+                    copied += b - a;
+                    busy[k] = true;
+                    if (trace) t_copy.push_back({now_us(), (double)((y1 - y0) * row_bytes) / 1e6});
+                    break;
+                }
+                a = b;
+            }
+        }
+    }
+    cudaError_t ce = cudaSuccess;
+    for (int k = 0; k < n_streams; k++) {
+        cudaError_t e = cudaStreamSynchronize(s->copy_stream[k]);
+        if (e != cudaSuccess) ce = e;
+    }
+    if (trace && !t_row.empty()) {
+        const size_t n = t_row.size();
+        std::fprintf(stderr, "dma: rows seen at us: first %.0f, 10%% %.0f, 25%% %.0f, 50%% %.0f, 75%% %.0f, 90%% %.0f, last %.0f; all copied at %.0f; %zu copies:", t_row[0],
+                     t_row[n / 10], t_row[n / 4], t_row[n / 2], t_row[3 * n / 4], t_row[9 * n / 10], t_row[n - 1], now_us(), t_copy.size());
+        for (auto& c : t_copy) std::fprintf(stderr, " %.0f:%.1fMB", c.first, c.second);
+        std::fprintf(stderr, "\n");
+    }
+    rc = collect(rc);
+    if (cerr) return cerr;
+    if (ce != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(ce));
+    return rc;
+}
+
 // Pinned, device-mapped host memory for canvases (rtc_b200.h).
 void* rtc_host_alloc(size_t nbytes) {
     void* p = nullptr;
@@ -1187,6 +1426,17 @@ void* rtc_host_alloc(size_t nbytes) {
 }
 void rtc_host_free(void* p) {
     if (p) cudaFreeHost(p);
+}
+
+// How a frame reaches a canvas in pinned host memory.  RTC_HOST_COPY=dma (default): render_to_pinned; warps: the
+// kernel's copy warps where the link time matters, else direct; direct: the render warps store into the mapped canvas.
+static int host_copy_mode() {
+    static const int mode = [] {
+        const char* e = std::getenv("RTC_HOST_COPY");
+        const std::string v = e ? e : "dma";
+        return v == "warps" ? 1 : v == "direct" ? 2 : 0;
+    }();
+    return mode;
 }
 
 // The device-side address of a pinned + mapped host buffer, or NULL for pageable memory.
@@ -1213,9 +1463,11 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
     // across PCIe, overlapped with the rendering of the others -- no staging frame, no copy afterwards.
     const bool whole = !part || part->n_parts <= 1;
     if (void* mapped = mapped_device_pointer(rgb_out)) {
+        const bool tiles_ok = whole || part->tile_rows % RTC_TILE_H == 0;  // a row of tiles lies together in the frame
+        if (host_copy_mode() == 0 && tiles_ok && s->replicas.empty()) return render_to_pinned(s, cam, max_depth, part, rgb_out, 3 * sizeof(double), stats);
         static const bool decouple = [] {
             const char* e = std::getenv("RTC_COPY_CTAS");
-            return !(e && std::atoi(e) == 0);
+            return !(e && std::atoi(e) == 0) && host_copy_mode() != 2;
         }();
         // ... where moving the frame is a large part of it: a frame whose kernel takes more than twice as long as the
         // link needs for its bytes (cover.json 1080p: 2.1 ms against 0.95) gains nothing from copy warps and loses their
@@ -1267,6 +1519,8 @@ int rtc_render_rgba8(rtc_scene* s, const rtc_camera* cam, int max_depth, const r
     // as rtc_render: a pinned + mapped buffer (rtc_host_alloc; the lib.zig twin's pixel buffer is one) is written by
     // the kernel itself, 4 bytes per pixel over PCIe while the frame renders
     if (void* mapped = mapped_device_pointer(rgba_out)) {
+        const bool tiles_ok = !part || part->n_parts <= 1 || part->tile_rows % RTC_TILE_H == 0;
+        if (host_copy_mode() == 0 && tiles_ok && s->replicas.empty()) return render_to_pinned(s, cam, max_depth, part, rgba_out, 4, stats);
         Target tg;
         tg.rgba = static_cast<unsigned char*>(mapped);
         tg.full_frame = tg.spread_rows = true;

@@ -19,6 +19,8 @@
 // bucket is the tile order.  The mean comes from the render kernel (counters[6] = sum of all tile costs).
 #include <cuda_runtime.h>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "render_params.h"
 
 namespace rtc {
@@ -114,7 +116,90 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
     const unsigned pos = s_base[b] + s_warp[b][warp] + rank;
     order[pos] = i;
 }
+// Order for frames whose finished ROWS of tiles are moved to a host canvas while the rest renders (rtc_api.cu
+// render_to_pinned, copy warps).  What such a frame needs is a link that is never idle: finished rows at least as fast as
+// the link takes them, from the first microseconds to the end of the kernel.  Two things stand in the way (measured on
+// dragons.json 1080p, tools/order_sim.py replays them from the recorded tile costs):
+//   * a row is complete only when its most expensive tile is, and in memory order that tile holds its row back by its
+//     own duration (tiles of 130-500 us in a 0.9 ms frame) -> every tile is started AHEAD of its row by what it costs;
+//   * the work is not spread evenly over the rows (dragons: the top 50 and bottom 50 rows of 270 hold 6 % of the work,
+//     the middle 110 rows 80 %): top to bottom, the cheap rows at the bottom arrive last, together with the expensive
+//     ones before them, and the link has a quarter of the frame left when the kernel ends -> the rows are taken in
+//     BANDS of a few rows (one copy each), cheapest band first: cheap bands keep the link busy while the expensive
+//     tiles, started at once because they are due so far ahead, work through their chains.
+// key = position of the tile's row in that sequence - cost x (rows the frame advances per unit of cost); a stable sort
+// by key.  The frame advances R rows in sum / W units of cost (W warps side by side; `lead` = W x a tuning factor).
+__global__ void band_work_kernel(const unsigned* __restrict__ cost, unsigned n, unsigned per_band, unsigned long long* __restrict__ band_work) {
+    __shared__ unsigned long long s_sum[32];
+    const unsigned first = blockIdx.x * per_band, last = min(first + per_band, n);
+    unsigned long long acc = 0;
+    for (unsigned i = first + threadIdx.x; i < last; i += blockDim.x) acc += cost[i];
+    for (int s = 16; s > 0; s >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, s);
+    if ((threadIdx.x & 31u) == 0) s_sum[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
+        for (unsigned w = 0; w < blockDim.x / 32; w++) t += s_sum[w];
+        band_work[blockIdx.x] = t;
+    }
+}
+// seq[row] = place of the row in the sequence: bands by ascending work (ties: top first), the rows of a band together
+__global__ void band_rank_kernel(const unsigned long long* __restrict__ band_work, unsigned n_bands, unsigned band_rows, unsigned n_rows,
+                                 unsigned* __restrict__ seq) {
+    for (unsigned b = threadIdx.x; b < n_bands; b += blockDim.x) {
+        const unsigned long long w = band_work[b];
+        unsigned rows_before = 0;
+        for (unsigned j = 0; j < n_bands; j++) {
+            const unsigned long long wj = band_work[j];
+            if (wj < w || (wj == w && j < b)) rows_before += min(band_rows, n_rows - j * band_rows);
+        }
+        for (unsigned r = b * band_rows; r < min((b + 1) * band_rows, n_rows); r++) seq[r] = rows_before + (r - b * band_rows);
+    }
+}
+__global__ void row_key_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p, unsigned n, unsigned tiles_x,
+                               unsigned n_rows, unsigned lead, const unsigned* __restrict__ seq, unsigned* __restrict__ keys,
+                               unsigned* __restrict__ vals) {
+    const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned long long sum = *sum_p;
+    const unsigned row = seq[i / tiles_x];
+    // cost < 2^32, n_rows x lead < 2^31
+    const unsigned long long ahead = sum ? ((unsigned long long)cost[i] * ((unsigned long long)n_rows * lead)) / sum : 0ull;
+    keys[i] = ahead < row ? row - (unsigned)ahead : 0u;
+    vals[i] = i;
+}
 }  // namespace
+
+size_t row_order_temp_bytes(unsigned n_tiles) {
+    size_t bytes = 0;
+    unsigned* p = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, p, p, p, p, (int)n_tiles, 0, 32);
+    return bytes;
+}
+// words of `work` for a frame of n_tiles tiles in rows of tiles_x
+size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x) {
+    const size_t n_rows = (n_tiles + tiles_x - 1) / tiles_x;
+    return 3 * (size_t)n_tiles + 3 * n_rows + 8;  // keys, sorted keys, tile numbers; seq[n_rows]; band_work[<= n_rows] (64-bit)
+}
+
+// lead = warps working side by side (x a tuning factor); band_rows = rows of tiles per band
+int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned n_tiles, unsigned tiles_x,
+                     unsigned band_rows, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream) {
+    if (!n_tiles) return 0;
+    const unsigned n_rows = (n_tiles + tiles_x - 1) / tiles_x;
+    if (band_rows < 1) band_rows = 1;
+    const unsigned n_bands = (n_rows + band_rows - 1) / band_rows;
+    unsigned *keys = work, *keys_out = work + n_tiles, *vals = work + 2 * (size_t)n_tiles, *seq = work + 3 * (size_t)n_tiles;
+    unsigned long long* band_work = reinterpret_cast<unsigned long long*>(work + ((3 * (size_t)n_tiles + n_rows + 1) & ~size_t(1)));
+    band_work_kernel<<<n_bands, 256, 0, stream>>>(cost, n_tiles, band_rows * tiles_x, band_work);
+    band_rank_kernel<<<1, 256, 0, stream>>>(band_work, n_bands, band_rows, n_rows, seq);
+    row_key_kernel<<<(n_tiles + 255) / 256, 256, 0, stream>>>(cost, sum, n_tiles, tiles_x, n_rows, lead, seq, keys, vals);
+    int bits = 1;
+    while ((1u << bits) < n_rows) bits++;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys, keys_out, vals, order, (int)n_tiles, 0, bits, stream);
+    if (e != cudaSuccess) return (int)e;
+    return (int)cudaGetLastError();
+}
 
 // scratch: 4 * ceil(n_tiles / 1024) + 3 unsigned (the last three receive the number of tiles that cost >= 8x, 4x, 2x the mean); sum: the render kernel's sum of all tile costs (device memory)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,

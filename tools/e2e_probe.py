@@ -37,8 +37,28 @@ def main():
     host[:] = 0.0  # the steady-state path really delivers the frame
     st = cam.render(wld, out=host).stats
     assert np.array_equal(host, ref), "steady-state frame did not reach the pinned canvas"
-    print("%s %dx%d copy_ctas=%s: e2e %.4f ms/frame, kernel %.4f ms (%s), %.1f Mrays/s" % (
-        name, w, h, os.environ.get("RTC_COPY_CTAS", "default"), ms, k_ms / n, ("mega", "wave", "mixed")[st.kernel], st.rays / ms / 1e3))
+    print("%s %dx%d host_copy=%s copy_ctas=%s: e2e %.4f ms/frame, kernel %.4f ms (%s), %.1f Mrays/s" % (
+        name, w, h, os.environ.get("RTC_HOST_COPY", "default"), os.environ.get("RTC_COPY_CTAS", "default"), ms, k_ms / n,
+        ("mega", "wave", "mixed")[st.kernel], st.rays / ms / 1e3))
+    # the lib.zig twin: RGBA8 into pinned memory
+    import ctypes
+    staged, _ = cam.render_rgba8(wld)
+    pin8 = pkg.pinned_empty((h, w, 4), dtype=np.uint8)
+    stt = pkg.rtc_stats()
+
+    def once():
+        pkg._check(pkg.lib().rtc_render_rgba8(wld._h, ctypes.byref(cam.c), 5, None, pin8.ctypes.data, ctypes.byref(stt)))
+    for _ in range(8):
+        once()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(n):
+        once()
+    ms8 = (time.perf_counter() - t0) / n * 1e3
+    pin8[:] = 0
+    once()
+    assert np.array_equal(pin8, staged), "RGBA8 frame in pinned memory differs from the staged one"
+    print("%s %dx%d rgba8: e2e %.4f ms/frame, kernel %.4f ms" % (name, w, h, ms8, stt.kernel_ms))
 
 
 if __name__ == "__main__":

@@ -64,6 +64,12 @@ def main():
                                    "top10": [round(float(x), 1) for x in top[:10]], "over_100us": int((c > 100).sum()),
                                    "over_50us": int((c > 50).sum()), "mean": round(float(c.mean()), 2),
                                    "note": "a heavy tile in the mixed kernel is worked on by four warps: its cost is their sum"}
+            if os.environ.get("RTC_DUMP_COSTS"):  # the tile costs of the last recorded frame (RTC_LPT_ALWAYS=1), for offline scheduling studies
+                import numpy as np
+                torch.cuda.synchronize()
+                n_tiles = ((cam.hsize + 7) // 8) * ((cam.vsize + 3) // 4)
+                both = bufs[0].view(2, words)[:, :n_tiles].cpu().numpy().astype(np.uint32)
+                np.save(os.environ["RTC_DUMP_COSTS"], both[0] if both[0].sum() > 0 else both[1])
             print(json.dumps(line), flush=True)
             for w in worlds:
                 w.close()
