@@ -570,10 +570,12 @@ def main():
             "value": value, "ms_per_step": dev_ms / args.steps,
             "e2e": {"value": e_rays_all / e_secs / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * e_secs / args.steps,
                     "h2d_bytes_per_step": int(ctypes_sizeof_camera(pkg)), "d2h_bytes_per_step": int(HEIGHT * WIDTH * 24),
-                    "canvas": "page-locked host memory (rtc_host_alloc): the kernel stores finished pixels into it over "
-                              "PCIe while rendering" if world == 1 else (
+                    "canvas": "page-locked host memory (rtc_host_alloc): the kernel renders into device memory and announces "
+                              "every finished row of tiles; the calling thread hands runs of them to the copy engine while the "
+                              "rest renders (rtc_api.cu render_to_pinned)" if world == 1 else (
                                   "one shared-memory host canvas, page-locked in every rank (cudaHostRegister): each rank's "
-                                  "Camera.render(world, partition) stores its rows into it over its own PCIe link, then a barrier"
+                                  "Camera.render(world, partition) moves its rows into it over its own PCIe link (copy engine, "
+                                  "while the rest renders), then a barrier"
                                   if shared is not None else "rank 0 copies the assembled frame to pinned memory"),
                     "pageable_canvas_ms_per_step": (1e3 * p_secs / args.steps) if p_secs else None,
                     "d2h_copy_floor_ms": d2h_ms,
@@ -606,8 +608,8 @@ def main():
         if r8_secs:
             line["e2e_rgba8"] = {"value": rays_all / r8_secs / 1e6, "unit": "Mrays/s",
                                  "ms_per_step": 1e3 * r8_secs / args.steps, "d2h_bytes_per_step": int(HEIGHT * WIDTH * 4),
-                                 "call": "rtc_render_rgba8 (lib.zig:135-155 twin) into a pinned buffer: the kernel stores clamp()ed "
-                                         "pixels straight into host memory"}
+                                 "call": "rtc_render_rgba8 (lib.zig:135-155 twin) into a pinned buffer: clamp()ed pixels, moved by the "
+                                         "copy engine row by row of tiles while the frame renders"}
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             r, s, desc, sc = cpu_frame(SCENE, WIDTH, HEIGHT, threads)

@@ -169,7 +169,7 @@ int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsig
 size_t row_order_temp_bytes(unsigned n_tiles);
 size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x);
 int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned n_tiles, unsigned tiles_x,
-                     unsigned band_rows, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream);
+                     unsigned band_rows, int by_work, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream);
 
 // render_inst_*.cu: the instantiations of render_kernel<MESH, LPP, FEAT>, one translation unit per (MESH, FEAT).
 // smem = dynamic shared memory per CTA (parked state + the BVH traversal stacks).

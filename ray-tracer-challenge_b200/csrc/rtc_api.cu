@@ -102,7 +102,8 @@ struct rtc_scene {
         rtc_camera cam;
         int depth;
         unsigned tile_rows, part, n_parts, deal_rank, deal_n;
-        int last_bucket;  // tile_order.cu: how many cost buckets the order distinguishes
+        int last_bucket;  // tile_order.cu: how many cost buckets the order distinguishes; < 0: bands of -last_bucket rows (launch_row_order)
+        int by_work;      // ... cheapest band first (1) or top to bottom (0)
     };
     size_t pending = 0;         // tiles the last frame recorded costs for (0: none), in cost buffer (parity ^ 1)
     View pending_view{};        // ... and the view it rendered
@@ -813,6 +814,13 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             measuring = true;
         } else {
             which = (!dealt && s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
+            // A frame that is moved to a host canvas while it renders (rows announced, or copy warps): only the megakernel
+            // finishes rows before the end.  The wavefront frame is copied afterwards, kernel + link, where the megakernel's
+            // costs about max(kernel, link) (csg.json 2160p: wavefront 1.59 + 3.6 ms against megakernel 1.6 beside 3.6).
+            if (which == 1 && (tg.announce || tg.copy_out) && s->best_ms[0] > 0.0f) {
+                const double link_ms = (double)P.rows * cam->hsize * (tg.rgba ? 4.0 : 24.0) / 55e6;
+                if (s->best_ms[1] + link_ms > 1.05 * std::max((double)s->best_ms[0], link_ms)) which = 0;
+            }
             if (three)
                 for (int k = 2; k < 5; k++)
                     if (s->best_ms[k] >= 0.0f && s->best_ms[k] < s->best_ms[which]) which = k;
@@ -960,6 +968,15 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
                 size_t band = std::max<size_t>(1, ((size_t)band_kb << 10) / tile_row_bytes);
                 if (P.n_parts > 1) band = std::max<size_t>(1, P.tile_rows / RTC_TILE_H);
                 view.last_bucket = -(int)std::min<size_t>(band, 4096);
+                // cheapest band first where the kernel takes about as long as the link (the link must never wait); top to
+                // bottom where the link takes much longer anyway and long runs of neighbouring rows serve it best (measured:
+                // teapot 1080p 0.99 against 1.03 ms, skybox 2160p 3.62 against 3.83; dragons 1.24 against 1.10)
+                static const int forced_seq = [] {
+                    const char* e = std::getenv("RTC_BAND_BY_WORK");
+                    return e ? std::atoi(e) : -1;
+                }();
+                const double link_ms = (double)P.rows * cam->hsize * (tg.rgba ? 4.0 : 24.0) / 55e6;
+                view.by_work = forced_seq >= 0 ? (forced_seq != 0) : !(s->best_ms[0] > 0.0f && link_ms > 1.4 * s->best_ms[0]);
             }
         }
         if (s->pending == n_tiles && s->pending_view.last_bucket < 0) {
@@ -980,7 +997,7 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             const unsigned lead = (unsigned)((unsigned long long)s->grid * (RTC_BLOCK_THREADS / 32) * lead_pct / 100u);
             void* temp = reinterpret_cast<char*>(s->d_row_work) + (((3 * s->row_work_cap + 3 * (s->row_work_cap + 8) + 8) * sizeof(unsigned) + 255) & ~size_t(255));
             CUDA_TRY((cudaError_t)launch_row_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
-                                                   s->d_row_work, s->d_tile_order, (unsigned)n_tiles, P.tiles_x, (unsigned)-s->pending_view.last_bucket, lead,
+                                                   s->d_row_work, s->d_tile_order, (unsigned)n_tiles, P.tiles_x, (unsigned)-s->pending_view.last_bucket, s->pending_view.by_work, lead,
                                                    temp, s->row_temp_bytes, stream));
             s->order_tiles = n_tiles;
             s->order_view = s->pending_view;
@@ -1434,7 +1451,7 @@ static int host_copy_mode() {
     static const int mode = [] {
         const char* e = std::getenv("RTC_HOST_COPY");
         const std::string v = e ? e : "dma";
-        return v == "warps" ? 1 : v == "direct" ? 2 : 0;
+        return v == "warps" ? 1 : v == "direct" ? 2 : 0;  // (dma_all: as dma, row partitions included)
     }();
     return mode;
 }
@@ -1463,8 +1480,16 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
     // across PCIe, overlapped with the rendering of the others -- no staging frame, no copy afterwards.
     const bool whole = !part || part->n_parts <= 1;
     if (void* mapped = mapped_device_pointer(rgb_out)) {
+        // whole frames: the copy engine (render_to_pinned).  Row partitions (N processes filling one shared canvas) lie in
+        // blocks of tile_rows scanlines, too small for a copy of their own (3.5 us of set-up each): the kernel's copy warps
+        // move those (measured at 2 GPUs, e2e: 0.79 ms against 0.99; RTC_HOST_COPY=dma_all sends them to the copy engine too)
         const bool tiles_ok = whole || part->tile_rows % RTC_TILE_H == 0;  // a row of tiles lies together in the frame
-        if (host_copy_mode() == 0 && tiles_ok && s->replicas.empty()) return render_to_pinned(s, cam, max_depth, part, rgb_out, 3 * sizeof(double), stats);
+        static const bool dma_parts = [] {
+            const char* e = std::getenv("RTC_HOST_COPY");
+            return e && std::string(e) == "dma_all";
+        }();
+        if (host_copy_mode() == 0 && (whole || dma_parts) && tiles_ok && s->replicas.empty())
+            return render_to_pinned(s, cam, max_depth, part, rgb_out, 3 * sizeof(double), stats);
         static const bool decouple = [] {
             const char* e = std::getenv("RTC_COPY_CTAS");
             return !(e && std::atoi(e) == 0) && host_copy_mode() != 2;
@@ -1519,8 +1544,8 @@ int rtc_render_rgba8(rtc_scene* s, const rtc_camera* cam, int max_depth, const r
     // as rtc_render: a pinned + mapped buffer (rtc_host_alloc; the lib.zig twin's pixel buffer is one) is written by
     // the kernel itself, 4 bytes per pixel over PCIe while the frame renders
     if (void* mapped = mapped_device_pointer(rgba_out)) {
-        const bool tiles_ok = !part || part->n_parts <= 1 || part->tile_rows % RTC_TILE_H == 0;
-        if (host_copy_mode() == 0 && tiles_ok && s->replicas.empty()) return render_to_pinned(s, cam, max_depth, part, rgba_out, 4, stats);
+        const bool whole8 = !part || part->n_parts <= 1;
+        if (host_copy_mode() == 0 && whole8 && s->replicas.empty()) return render_to_pinned(s, cam, max_depth, part, rgba_out, 4, stats);
         Target tg;
         tg.rgba = static_cast<unsigned char*>(mapped);
         tg.full_frame = tg.spread_rows = true;

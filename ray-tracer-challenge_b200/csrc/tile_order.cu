@@ -144,8 +144,14 @@ __global__ void band_work_kernel(const unsigned* __restrict__ cost, unsigned n, 
     }
 }
 // seq[row] = place of the row in the sequence: bands by ascending work (ties: top first), the rows of a band together
+// (by_work == 0: top to bottom -- frames whose link time is well above their kernel time: there the link is busy anyway
+// and wants long runs of neighbouring rows, not the cheapest ones)
 __global__ void band_rank_kernel(const unsigned long long* __restrict__ band_work, unsigned n_bands, unsigned band_rows, unsigned n_rows,
-                                 unsigned* __restrict__ seq) {
+                                 int by_work, unsigned* __restrict__ seq) {
+    if (!by_work) {
+        for (unsigned r = threadIdx.x; r < n_rows; r += blockDim.x) seq[r] = r;
+        return;
+    }
     for (unsigned b = threadIdx.x; b < n_bands; b += blockDim.x) {
         const unsigned long long w = band_work[b];
         unsigned rows_before = 0;
@@ -184,15 +190,15 @@ size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x) {
 
 // lead = warps working side by side (x a tuning factor); band_rows = rows of tiles per band
 int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned n_tiles, unsigned tiles_x,
-                     unsigned band_rows, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream) {
+                     unsigned band_rows, int by_work, unsigned lead, void* temp, size_t temp_bytes, cudaStream_t stream) {
     if (!n_tiles) return 0;
     const unsigned n_rows = (n_tiles + tiles_x - 1) / tiles_x;
     if (band_rows < 1) band_rows = 1;
     const unsigned n_bands = (n_rows + band_rows - 1) / band_rows;
     unsigned *keys = work, *keys_out = work + n_tiles, *vals = work + 2 * (size_t)n_tiles, *seq = work + 3 * (size_t)n_tiles;
     unsigned long long* band_work = reinterpret_cast<unsigned long long*>(work + ((3 * (size_t)n_tiles + n_rows + 1) & ~size_t(1)));
-    band_work_kernel<<<n_bands, 256, 0, stream>>>(cost, n_tiles, band_rows * tiles_x, band_work);
-    band_rank_kernel<<<1, 256, 0, stream>>>(band_work, n_bands, band_rows, n_rows, seq);
+    if (by_work) band_work_kernel<<<n_bands, 256, 0, stream>>>(cost, n_tiles, band_rows * tiles_x, band_work);
+    band_rank_kernel<<<1, 256, 0, stream>>>(band_work, n_bands, band_rows, n_rows, by_work, seq);
     row_key_kernel<<<(n_tiles + 255) / 256, 256, 0, stream>>>(cost, sum, n_tiles, tiles_x, n_rows, lead, seq, keys, vals);
     int bits = 1;
     while ((1u << bits) < n_rows) bits++;
