@@ -126,6 +126,12 @@ __device__ __forceinline__ void copy_finished_rows(const RenderParams& P) {
 #ifndef RTC_MIN_BLOCKS_ANALYTIC
 #define RTC_MIN_BLOCKS_ANALYTIC 6
 #endif
+// ... analytic scenes that need CSG or the general pattern evaluator (FEAT != 0): 5 (96 registers).  Measured on B200, kernel
+// ms at 6 / 5 / 4 CTAs per SM: csg.json 2160p 1.472 / 1.398 / 1.406, skybox.json 2160p 1.257 / 1.228 / 1.280; the lean
+// instantiation: fresnel 600^2 0.530 / 0.505 / 0.517 but cover.json 1080p 2.044 / 2.201 / 2.347 -- it stays at 6.
+#ifndef RTC_MIN_BLOCKS_ANALYTIC_GENERAL
+#define RTC_MIN_BLOCKS_ANALYTIC_GENERAL 5
+#endif
 #ifndef RTC_MIN_BLOCKS_MESH
 #define RTC_MIN_BLOCKS_MESH 4
 #endif
@@ -144,8 +150,14 @@ __device__ __forceinline__ void copy_finished_rows(const RenderParams& P) {
 // An instantiation carries only what its scene needs: fewer instructions to fetch (the render loop is larger than the
 // instruction cache: stall_no_instruction leads the ncu captures), no calls in the loop, fewer live registers.  FEAT = 0
 // ("lean") serves 9 of the 14 shipped scenes, dragons / teapot / cover / fresnel among them.
+#ifdef RTC_MAXNREG_MESH  // experiment: an explicit register limit for the mesh instantiations instead of a CTA count
+#define RTC_KERNEL_BOUNDS __launch_bounds__(RTC_BLOCK) __maxnreg__(MESH ? RTC_MAXNREG_MESH : FEAT ? 96 : 80)
+#else
+#define RTC_KERNEL_BOUNDS \
+    __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : FEAT ? RTC_MIN_BLOCKS_ANALYTIC_GENERAL : RTC_MIN_BLOCKS_ANALYTIC)
+#endif
 template <bool MESH, int LPP, int FEAT>
-__global__ void __launch_bounds__(RTC_BLOCK, MESH ? RTC_MIN_BLOCKS_MESH : RTC_MIN_BLOCKS_ANALYTIC) render_kernel(DScene S, RenderParams P) {
+__global__ void RTC_KERNEL_BOUNDS render_kernel(DScene S, RenderParams P) {
     constexpr bool LEAN = (FEAT & RTC_FEAT_CSG) == 0;            // no CSG / guards / stray triangles
     constexpr bool SIMPLE_PAT = (FEAT & RTC_FEAT_PATTERNS) == 0;  // rt_pattern.cuh simple_pattern_color suffices
     static_assert(LPP == 1 || RTC_REFILL_MIN == 32, "lanes sharing a pixel rely on whole-warp refills");

@@ -34,7 +34,10 @@ constexpr int T = 1024;
 __device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum, int last) {
     if (sum == 0) return last;  // nothing measured (every tile below one tick): keep the plain order
     const unsigned long long c = (unsigned long long)cost * n;  // cost / mean = c / sum; cost < 2^32, n < 2^24
-    const int b = c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+#ifndef RTC_HEAVY_X
+#define RTC_HEAVY_X 8
+#endif
+    const int b = c >= RTC_HEAVY_X * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
     return b < last ? b : last;
 }
 

@@ -490,6 +490,35 @@ def test_rgba8_into_pinned_memory_is_zero_copy_and_equal(pkg):
     pkg.free_pinned(pinned)
 
 
+@pytest.mark.parametrize("w,h", [(163, 97), (7, 5), (1, 1), (640, 363)])
+def test_pinned_canvas_through_the_copy_engine(pkg, w, h):
+    """rtc_render / rtc_render_rgba8 into rtc_host_alloc memory: the kernel announces finished rows of tiles and the calling
+    thread hands them to the copy engine while the rest renders (rtc_api.cu render_to_pinned).  Same frame as the staged
+    path bit for bit -- ragged sizes, the first frames (no order yet, kernel measurement, wavefront frames copied
+    afterwards), a camera that moves every frame (new band order every frame), f64 and RGBA8 alternating."""
+    import ctypes
+    info = pkg.parse_scene(scenes.SMOKE_SCENE, "", w, h)
+    cam, wld = info.camera, info.world
+    pinned = pkg.pinned_empty((h, w, 3))
+    pin8 = pkg.pinned_empty((h, w, 4), dtype=np.uint8)
+    st = pkg.rtc_stats()
+    for k in range(14):
+        if k >= 8:
+            cam.look_at((0.3 * (k - 8), 2.5, -7), (0, 0.8, 0), (0, 1, 0))
+        want = cam.render(wld).pixels          # pageable canvas: staged, one copy afterwards
+        want8, _ = cam.render_rgba8(wld)
+        pinned[:] = np.nan
+        got = cam.render(wld, out=pinned)
+        assert np.array_equal(pinned, want), (w, h, k)
+        assert got.stats.primary_rays == w * h
+        pin8[:] = 0
+        pkg._check(pkg.lib().rtc_render_rgba8(wld._h, ctypes.byref(cam.c), 5, None, pin8.ctypes.data, ctypes.byref(st)))
+        assert np.array_equal(pin8, want8), (w, h, k)
+    pkg.free_pinned(pinned)
+    pkg.free_pinned(pin8)
+    wld.close()
+
+
 def test_replicated_scene_uses_all_devices(pkg):
     """rtc_set_devices(n): ONE process, the scene built once and replicated, a whole-frame call split over the devices
     (interleaved 8-row tiles, peer stores into device 0's frame / into the caller's pinned canvas): bit-identical."""
