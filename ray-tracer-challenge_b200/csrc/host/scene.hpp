@@ -86,7 +86,14 @@ struct Pattern {
 inline PatternP share(Pattern p) { return std::make_shared<const Pattern>(std::move(p)); }
 
 struct Material {
-    PatternP pattern = share(Pattern::solid({1, 1, 1}));
+    // (one immutable default pattern for every Material: a scene constructs hundreds of thousands of Materials -- one per
+    // triangle, overwritten when the object's material is stamped on -- and allocating a pattern for each was a tenth of
+    // the load time)
+    static const PatternP& default_pattern() {
+        static const PatternP p = share(Pattern::solid({1, 1, 1}));
+        return p;
+    }
+    PatternP pattern = default_pattern();
     double ambient = 0.1, diffuse = 0.9, specular = 0.9, shininess = 200.0;
     double reflective = 0.0, transparency = 0.0, refractive_index = 1.0;
 };
