@@ -111,8 +111,9 @@ def lib():
     L.rtc_render_rgba8.argtypes = common + [vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_device.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
     L.rtc_render_device_frame.argtypes = common + [vp, vp, ctypes.POINTER(rtc_stats)]
-    L.rtc_static_max_tiles.restype = ctypes.c_uint64
-    L.rtc_render_device_static.argtypes = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, vp, vp, ctypes.POINTER(rtc_stats)]
+    if hasattr(L, "rtc_static_max_tiles"):  # (absent in older builds that tools/kernel_variants.py compares against)
+        L.rtc_static_max_tiles.restype = ctypes.c_uint64
+        L.rtc_render_device_static.argtypes = [vp, ctypes.POINTER(rtc_camera), ctypes.c_int, vp, vp, ctypes.POINTER(rtc_stats)]
     L.rtc_partition_rows.argtypes = [ctypes.c_uint64, ctypes.POINTER(rtc_partition)]
     L.rtc_partition_rows.restype = ctypes.c_uint64
     L.rtc_load_scene_json.argtypes = [cp, cp, ctypes.c_long, ctypes.c_long, ctypes.POINTER(vp),

@@ -271,10 +271,6 @@ __global__ void RTC_KERNEL_BOUNDS render_kernel(DScene S, RenderParams P) {
         if (__popc(need) < RTC_REFILL_MIN && __any_sync(0xffffffffu, state != ST_IDLE)) need = 0;
 #endif
         if (need) {
-            // the next items first: the round trip of this atomic overlaps the release of the finished tile below
-            unsigned long long base = 0;
-            const int leader = __ffs(need) - 1;
-            if ((int)lane == leader) base = atomicAdd(P.counters, (unsigned long long)__popc(need));
             // cost of the tile this warp is through with (clock ticks / 64), for the order of the NEXT frame
             // (added to the cost arrays of all renderers sharing the frame, so that all copies stay equal)
             if (LPP == 1 && P.copy_out) __syncwarp();  // every lane's pixel stores before lane 0 announces the tile
@@ -303,6 +299,9 @@ __global__ void RTC_KERNEL_BOUNDS render_kernel(DScene S, RenderParams P) {
                 }
                 PK(PK_SPARE) = -1.0;
             }
+            unsigned long long base = 0;
+            const int leader = __ffs(need) - 1;
+            if ((int)lane == leader) base = atomicAdd(P.counters, (unsigned long long)__popc(need));
             base = __shfl_sync(0xffffffffu, base, leader);
             if (state == ST_IDLE && !done) {
                 unsigned long long item = base + __popc(need & lt_mask);

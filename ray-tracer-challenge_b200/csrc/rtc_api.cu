@@ -814,16 +814,17 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             measuring = true;
         } else {
             which = (!dealt && s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
-            // A frame that is moved to a host canvas while it renders (rows announced, or copy warps): only the megakernel
-            // finishes rows before the end.  The wavefront frame is copied afterwards, kernel + link, where the megakernel's
-            // costs about max(kernel, link) (csg.json 2160p: wavefront 1.59 + 3.6 ms against megakernel 1.6 beside 3.6).
-            if (which == 1 && (tg.announce || tg.copy_out) && s->best_ms[0] > 0.0f) {
-                const double link_ms = (double)P.rows * cam->hsize * (tg.rgba ? 4.0 : 24.0) / 55e6;
-                if (s->best_ms[1] + link_ms > 1.05 * std::max((double)s->best_ms[0], link_ms)) which = 0;
-            }
             if (three)
                 for (int k = 2; k < 5; k++)
                     if (s->best_ms[k] >= 0.0f && s->best_ms[k] < s->best_ms[which]) which = k;
+            // A frame that is moved to a host canvas while it renders (rows announced, or copy warps): only the megakernel
+            // with one lane per pixel finishes rows before the end.  A wavefront frame, or one with several lanes per pixel,
+            // is copied afterwards, kernel + link, where the megakernel's costs about max(kernel, link) (csg.json 2160p:
+            // wavefront 1.59 + 3.6 ms against megakernel 1.6 beside 3.6).
+            if (which != 0 && (tg.announce || tg.copy_out) && s->best_ms[0] > 0.0f) {
+                const double link_ms = (double)P.rows * cam->hsize * (tg.rgba ? 4.0 : 24.0) / 55e6;
+                if (s->best_ms[which] + link_ms > 1.05 * std::max((double)s->best_ms[0], link_ms)) which = 0;
+            }
         }
     }
     int lpp = forced_lpp(s);
@@ -1494,12 +1495,10 @@ int rtc_render(rtc_scene* s, const rtc_camera* cam, int max_depth, const rtc_par
             const char* e = std::getenv("RTC_COPY_CTAS");
             return !(e && std::atoi(e) == 0) && host_copy_mode() != 2;
         }();
-        // ... where moving the frame is a large part of it: a frame whose kernel takes more than twice as long as the
-        // link needs for its bytes (cover.json 1080p: 2.1 ms against 0.95) gains nothing from copy warps and loses their
-        // CTAs -- there the render warps store into the canvas themselves, as partitions and replicated scenes do
-        const uint64_t my_rows = rtc_partition_rows(cam->vsize, part);
-        const double link_ms = (double)my_rows * cam->hsize * 24.0 / 52e6;  // ~52 GB/s measured for SM-written host memory
-        const bool worth = s->best_ms[0] < 0.0f || link_ms >= 0.5 * s->best_ms[0];
+        // (Until the per-tile fence was found to drop the L1, this path was used only where the link time was at least half
+        // the kernel time.  Since then it wins everywhere -- the direct stores also cost the frame its cost order: a 1/4
+        // partition of dragons 1080p 0.80 ms with direct stores, its kernel in cost order 0.42 -- so it is unconditional.)
+        const bool worth = true;
         const bool rows_ok = whole || part->tile_rows % RTC_TILE_H == 0;  // a row of tiles lies together in the frame
         if (decouple && worth && rows_ok && s->replicas.empty()) {
             // rendered into device memory (a frame-sized staging buffer, pixels at their frame positions) in cost order at
