@@ -385,7 +385,7 @@ def main():
         return []
 
     # ---- warm-up (untimed) ---------------------------------------------------------------------------------
-    for _ in range(max(args.warmup, 12)):  # the library measures its kernel candidates on the first five to eleven frames
+    for _ in range(max(args.warmup, 18)):  # the library measures its kernel candidates on the first five to fifteen frames
         step_device()
         drain()
     barrier()

@@ -163,8 +163,9 @@ int occupancy_wave_mesh(int* blocks_per_sm, size_t smem);
 int occupancy_wave_analytic(int* blocks_per_sm, size_t smem);
 int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 // tile_order.cu: order[] = the tiles 0..n_tiles-1, stably sorted into four cost buckets (most expensive first)
+#define RTC_ORDER_BUCKETS 8  // buckets at most; scratch = RTC_ORDER_BUCKETS x (blocks of 1024 tiles + 1) words
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
-                      int last_bucket, cudaStream_t stream);
+                      int last_bucket, int set, cudaStream_t stream);
 // ... or for frames streamed to a host canvas: bands of rows, cheapest band first, every tile started ahead of its row by what it costs
 size_t row_order_temp_bytes(unsigned n_tiles);
 size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x);

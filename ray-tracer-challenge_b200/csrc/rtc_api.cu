@@ -82,7 +82,7 @@ struct rtc_scene {
     int frames = 0;
     // [0] megakernel, [1] wavefront, [2..4] megakernel with four lanes per pixel on the tiles that cost >= 8x / 4x / 2x the
     // mean in the frame the order was made from (small partitions only, see mixed_candidate); per pixel-count of the last frame
-    float best_ms[5] = {-1.0f, -1.0f, -1.0f, -1.0f, -1.0f};
+    float best_ms[2 + RTC_ORDER_BUCKETS] = {-1.0f, -1.0f, -1.0f, -1.0f, -1.0f, -1.0f, -1.0f, -1.0f, -1.0f, -1.0f};  // ([2 ..]: one per threshold of the order's bucket set)
     size_t tuned_pixels = 0;
     // Tile order of the megakernel: frame k adds the cost of every tile to cost buffer k & 1; frame k + 1 first makes
     // the permutation out of it (tile_order.cu), clears it for frame k + 2, then renders in that order.  Two buffers,
@@ -104,6 +104,7 @@ struct rtc_scene {
         unsigned tile_rows, part, n_parts, deal_rank, deal_n;
         int last_bucket;  // tile_order.cu: how many cost buckets the order distinguishes; < 0: bands of -last_bucket rows (launch_row_order)
         int by_work;      // ... cheapest band first (1) or top to bottom (0)
+        int bucket_set;   // tile_order.cu: 0 = buckets at 8x / 4x / 2x the mean, 1 = at 12x / 8x / 7x / 6x / 4x / 2x (shared frames)
     };
     size_t pending = 0;         // tiles the last frame recorded costs for (0: none), in cost buffer (parity ^ 1)
     View pending_view{};        // ... and the view it rendered
@@ -207,9 +208,11 @@ static int forced_lpp(const rtc_scene* s) {
 // lights.  Measured on dragons.json 1080p, L2 flushed (kernel ms, one lane / two lanes / mixed): 1/4 partition
 // 0.46 / 0.45 / 0.36, 1/8 partition 0.48 / 0.39 / 0.33; 1/2 partition 0.58 / - / 0.63, whole frame 1.04 / 1.60 / 1.19
 // (profiles/README.md).
-static bool mixed_candidate(const rtc_scene* s, size_t n_px) {
+// Frames shared tile by tile (dealt): up to 16 tiles per warp -- a 1/2 share, whose time is its heaviest one-lane tile
+// (507 us of a 0.49 ms kernel) -- and six thresholds to choose from (tile_order.cu, set 1).
+static bool mixed_candidate(const rtc_scene* s, size_t n_px, bool dealt) {
     const size_t warps = (size_t)s->grid * (RTC_BLOCK_THREADS / 32);
-    return s->d.n_lights >= 2 && s->d.n_lights <= RTC_HEAVY_LANES - (RTC_HEAVY_LANES == 8 ? 1 : 0) && n_px / 32 < 8 * warps;
+    return s->d.n_lights >= 2 && s->d.n_lights <= RTC_HEAVY_LANES - (RTC_HEAVY_LANES == 8 ? 1 : 0) && n_px / 32 < (dealt ? 16 : 8) * warps;
 }
 
 extern "C" {
@@ -798,7 +801,8 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
     bool measuring = false;
     if (which < 0) {
         const int guess = 0;
-        const bool three = forced_lpp(s) < 0 && mixed_candidate(s, n_px);
+        const bool three = forced_lpp(s) < 0 && mixed_candidate(s, n_px, dealt);
+        const int n_thr = dealt ? 6 : 3;  // thresholds of the order's bucket set (tile_order.cu)
         // Frames 0-2: megakernel (the first is cold, the second makes the tile order, the third is what a steady frame
         // costs), frames 3-4: wavefront (the first loads its kernels), then -- small partitions -- two frames each with
         // the tiles that cost >= 8x, >= 4x, >= 2x the mean four-fold.  The best time of each candidate counts.
@@ -809,13 +813,13 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         } else if (s->frames < 5 && !dealt) {
             which = 1;
             measuring = true;
-        } else if (three && s->frames < (dealt ? 9 : 11)) {  // (a shared frame has no wavefront frames)
+        } else if (three && s->frames < (dealt ? 3 : 5) + 2 * n_thr) {  // (a shared frame has no wavefront frames)
             which = 2 + (s->frames - (dealt ? 3 : 5)) / 2;
             measuring = true;
         } else {
             which = (!dealt && s->best_ms[1] >= 0.0f && (s->best_ms[0] < 0.0f || s->best_ms[1] < s->best_ms[0])) ? 1 : 0;
             if (three)
-                for (int k = 2; k < 5; k++)
+                for (int k = 2; k < 2 + n_thr; k++)
                     if (s->best_ms[k] >= 0.0f && s->best_ms[k] < s->best_ms[which]) which = k;
             // A frame that is moved to a host canvas while it renders (rows announced, or copy warps): only the megakernel
             // with one lane per pixel finishes rows before the end.  A wavefront frame, or one with several lanes per pixel,
@@ -932,7 +936,7 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             if (s->d_tile_order) cudaFree(s->d_tile_order);
             s->d_scratch = s->d_tile_order = nullptr;
             s->order_cap = 0;
-            CUDA_TRY(cudaMalloc(&s->d_scratch, (4 * (n_tiles / 1024 + 1) + 3) * sizeof(unsigned)));
+            CUDA_TRY(cudaMalloc(&s->d_scratch, RTC_ORDER_BUCKETS * (n_tiles / 1024 + 2) * sizeof(unsigned)));
             CUDA_TRY(cudaMalloc(&s->d_tile_order, n_tiles * sizeof(unsigned)));
             s->order_cap = n_tiles;
             s->order_tiles = 0;
@@ -956,7 +960,8 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
             int v = e ? std::atoi(e) : -1;
             return v >= -1 && v <= 3 ? v : -1;
         }();
-        view.last_bucket = 3;
+        view.last_bucket = dealt ? 6 : 3;
+        view.bucket_set = dealt ? 1 : 0;
         if (tg.copy_out || tg.announce) {
             view.last_bucket = copy_buckets;
             if (copy_buckets < 0) {
@@ -1006,7 +1011,8 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         } else if (s->pending == n_tiles) {
             // the previous frame's costs (complete in EVERY renderer's copy: a shared frame ends with a barrier) -> the order
             CUDA_TRY((cudaError_t)launch_tile_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
-                                                    s->d_scratch, s->d_tile_order, (unsigned)n_tiles, s->pending_view.last_bucket, stream));
+                                                    s->d_scratch, s->d_tile_order, (unsigned)n_tiles, s->pending_view.last_bucket,
+                                                    s->pending_view.bucket_set, stream));
             s->order_tiles = n_tiles;
             s->order_view = s->pending_view;
             F.order_made = true;
@@ -1014,7 +1020,12 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
         if (s->pending) CUDA_TRY(cudaMemsetAsync(mine_prev, 0, s->share.words * sizeof(unsigned), stream));  // clean for its next turn
         s->pending = 0;
         P.tile_order = s->order_tiles == n_tiles ? s->d_tile_order : nullptr;
-        P.heavy_tiles = s->d_scratch + 4 * ((n_tiles + 1023) / 1024) + (which >= 2 ? which - 2 : 0);
+        static const int forced_idx = [] {  // with RTC_LPP=0: which threshold of the set (experiments)
+            const char* e = std::getenv("RTC_HEAVY_IDX");
+            int v = e ? std::atoi(e) : 0;
+            return v >= 0 && v < RTC_ORDER_BUCKETS - 1 ? v : 0;
+        }();
+        P.heavy_tiles = s->d_scratch + RTC_ORDER_BUCKETS * ((n_tiles + 1023) / 1024) + (which >= 2 ? which - 2 : forced_idx);
         static const bool always = [] {
             const char* e = std::getenv("RTC_LPT_ALWAYS");
             return e && e[0] == '1';
@@ -1619,7 +1630,7 @@ struct StaticScratch {
     unsigned long long counters[8];                              // RenderParams::counters
     unsigned cost[2][RTC_STATIC_MAX_TILES + 2];                  // tile costs + the 64-bit sum, two buffers taking turns
     unsigned order[RTC_STATIC_MAX_TILES];                        // RenderParams::tile_order
-    unsigned buckets[4 * (RTC_STATIC_MAX_TILES / 1024 + 1) + 3];  // tile_order.cu: bucket counts + heavy-tile counts
+    unsigned buckets[RTC_ORDER_BUCKETS * (RTC_STATIC_MAX_TILES / 1024 + 2)];  // tile_order.cu: bucket counts + heavy-tile counts
 };
 }  // namespace
 static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
@@ -1716,7 +1727,7 @@ int rtc_render_device_static(rtc_scene* s, const rtc_camera* cam, int max_depth,
     if (timed) CUDA_TRY(cudaEventRecord(s->ev0, stream));
     if (same_scene && st->pending == n_tiles) {
         CUDA_TRY((cudaError_t)launch_tile_order(prev, reinterpret_cast<const unsigned long long*>(prev + words - 2), sc->buckets, sc->order,
-                                                (unsigned)n_tiles, 3, stream));
+                                                (unsigned)n_tiles, 3, 0, stream));
         st->order_tiles = n_tiles;
         st->order_view = st->pending_view;
         order_made = true;
@@ -1724,7 +1735,7 @@ int rtc_render_device_static(rtc_scene* s, const rtc_camera* cam, int max_depth,
     if (st->pending) CUDA_TRY(cudaMemsetAsync(prev, 0, cost_words(st->pending) * sizeof(unsigned), stream));  // clean for its next turn
     st->pending = 0;
     P.tile_order = st->order_tiles == n_tiles ? sc->order : nullptr;
-    P.heavy_tiles = sc->buckets + 4 * ((n_tiles + 1023) / 1024);
+    P.heavy_tiles = sc->buckets + RTC_ORDER_BUCKETS * ((n_tiles + 1023) / 1024);
     if (!(P.tile_order && std::memcmp(&st->order_view, &view, sizeof view) == 0)) {
         P.cost_peer[0] = sc->cost[st->parity];
         P.cost_tiles = (unsigned)(words - 2);

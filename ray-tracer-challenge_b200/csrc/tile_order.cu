@@ -31,43 +31,48 @@ constexpr int T = 1024;
 // last: buckets beyond it are merged into it (last = 3: all four; last = 1: the tiles that cost >= 8x the mean, then ALL
 // others in their plain order -- frames whose finished tiles are streamed to a host canvas want the bulk of the tiles
 // in memory order, rtc_api.cu)
-__device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum, int last) {
+// set 0: the four buckets above.  set 1 (frames shared tile by tile between renderers, rtc_api.cu): seven buckets, cost >=
+// 12x, 8x, 7x, 6x, 4x, 2x the mean, the rest -- the counts of the leading buckets are the candidates for "how many tiles
+// get four lanes per pixel" (render_kernel.cuh MIXED), and which threshold is best depends on the size of the share:
+// tools/order_sim.py replays the recorded tile costs of dragons.json and predicts 12x for a 1/2 share, 6-8x for 1/4, 6x
+// for 1/8 (249 -> 199 us).
+constexpr int NB = 8;  // buckets at most
+__device__ __forceinline__ int bucket_of(unsigned cost, unsigned long long n, unsigned long long sum, int last, int set) {
     if (sum == 0) return last;  // nothing measured (every tile below one tick): keep the plain order
     const unsigned long long c = (unsigned long long)cost * n;  // cost / mean = c / sum; cost < 2^32, n < 2^24
-#ifndef RTC_HEAVY_X
-#define RTC_HEAVY_X 8
-#endif
-    const int b = c >= RTC_HEAVY_X * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+    int b;
+    if (set == 0) b = c >= 8 * sum ? 0 : c >= 4 * sum ? 1 : c >= 2 * sum ? 2 : 3;
+    else b = c >= 12 * sum ? 0 : c >= 8 * sum ? 1 : c >= 7 * sum ? 2 : c >= 6 * sum ? 3 : c >= 4 * sum ? 4 : c >= 2 * sum ? 5 : 6;
     return b < last ? b : last;
 }
 
 // counts[b * gridDim.x + block] = tiles of bucket b among the block's 1024
 __global__ void __launch_bounds__(T) tile_count_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
-                                                       unsigned* __restrict__ counts, unsigned n, int last) {
-    __shared__ unsigned s_cnt[4];
-    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
+                                                       unsigned* __restrict__ counts, unsigned n, int last, int set) {
+    __shared__ unsigned s_cnt[NB];
+    if (threadIdx.x < NB) s_cnt[threadIdx.x] = 0;
     __syncthreads();
     const unsigned i = blockIdx.x * T + threadIdx.x;
-    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last) : -1;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last, set) : -1;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
+    for (int k = 0; k < NB; k++) {
         const unsigned m = __ballot_sync(0xffffffffu, b == k);
         if ((threadIdx.x & 31u) == 0 && m) atomicAdd(&s_cnt[k], __popc(m));
     }
     __syncthreads();
-    if (threadIdx.x < 4) counts[threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
+    if (threadIdx.x < NB) counts[threadIdx.x * gridDim.x + blockIdx.x] = s_cnt[threadIdx.x];
 }
 
 __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restrict__ cost, const unsigned long long* __restrict__ sum_p,
                                                          const unsigned* __restrict__ counts, unsigned* __restrict__ order,
-                                                         unsigned* __restrict__ heavy, unsigned n, int last) {
-    __shared__ unsigned s_base[4];           // where this block's tiles of bucket b start
-    __shared__ unsigned s_start[5];          // where bucket b starts (s_start[4] = n)
-    __shared__ unsigned s_warp[4][T / 32];   // tiles of bucket b in each warp, then their exclusive prefix
+                                                         unsigned* __restrict__ heavy, unsigned n, int last, int set) {
+    __shared__ unsigned s_base[NB];           // where this block's tiles of bucket b start
+    __shared__ unsigned s_start[NB + 1];      // where bucket b starts (s_start[NB] = n)
+    __shared__ unsigned s_warp[NB][T / 32];   // tiles of bucket b in each warp, then their exclusive prefix
     __shared__ unsigned s_red[2][T / 32];
     const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     // flattened (bucket, block) index of this block's bucket b is b * gridDim.x + blockIdx.x: sum everything before it
-    for (int b = 0; b < 4; b++) {
+    for (int b = 0; b < NB; b++) {
         const unsigned first = b * gridDim.x, end = first + blockIdx.x;
         unsigned before = 0, mine = 0;  // tiles of the buckets before b (all blocks); tiles of bucket b in the blocks before this one
         for (unsigned j = tid; j < end; j += T) {
@@ -89,23 +94,20 @@ __global__ void __launch_bounds__(T) tile_scatter_kernel(const unsigned* __restr
         }
         __syncthreads();
     }
-    if (tid == 0) s_start[4] = n;
-    if (blockIdx.x == 0 && tid == 0) {
-        heavy[0] = s_start[1];  // tiles that cost >= 8x the mean
-        heavy[1] = s_start[2];  // ... >= 4x
-        heavy[2] = s_start[3];  // ... >= 2x
-    }
+    if (tid == 0) s_start[NB] = n;
+    if (blockIdx.x == 0 && tid == 0)
+        for (int k = 0; k + 1 < NB; k++) heavy[k] = s_start[k + 1];  // tiles that cost >= the k-th threshold (set 0: 8x, 4x, 2x the mean)
     const unsigned i = blockIdx.x * T + tid;
-    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last) : -1;
+    const int b = i < n ? bucket_of(cost[i], n, *sum_p, last, set) : -1;
     unsigned rank = 0;  // among the tiles of my bucket in my warp
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
+    for (int k = 0; k < NB; k++) {
         const unsigned m = __ballot_sync(0xffffffffu, b == k);
         if (b == k) rank = __popc(m & ((1u << lane) - 1u));
         if (lane == 0) s_warp[k][warp] = __popc(m);
     }
     __syncthreads();
-    if (warp < 4) {  // warp k: exclusive prefix over the 32 warp counts of bucket k
+    if (warp < NB) {  // warp k: exclusive prefix over the 32 warp counts of bucket k
         const unsigned c = s_warp[warp][lane];
         unsigned incl = c;
         for (int s = 1; s < 32; s <<= 1) {
@@ -210,13 +212,16 @@ int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsign
     return (int)cudaGetLastError();
 }
 
-// scratch: 4 * ceil(n_tiles / 1024) + 3 unsigned (the last three receive the number of tiles that cost >= 8x, 4x, 2x the mean); sum: the render kernel's sum of all tile costs (device memory)
+// scratch: RTC_ORDER_BUCKETS * ceil(n_tiles / 1024) + RTC_ORDER_BUCKETS unsigned (the last ones receive the number of tiles
+// that cost >= the set's thresholds: 8x, 4x, 2x the mean / 12x, 8x, 7x, 6x, 4x, 2x); sum: the render kernel's sum of all
+// tile costs (device memory); last_bucket: buckets beyond it are merged into it (set 0: <= 3, set 1: <= 6)
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
-                      int last_bucket, cudaStream_t stream) {
+                      int last_bucket, int set, cudaStream_t stream) {
+    static_assert(NB == RTC_ORDER_BUCKETS, "render_params.h RTC_ORDER_BUCKETS out of date");
     if (!n_tiles) return 0;
     const unsigned blocks = (n_tiles + T - 1) / T;
-    tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles, last_bucket);
-    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, scratch + 4 * blocks, n_tiles, last_bucket);
+    tile_count_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, n_tiles, last_bucket, set);
+    tile_scatter_kernel<<<blocks, T, 0, stream>>>(cost, sum, scratch, order, scratch + NB * blocks, n_tiles, last_bucket, set);
     return (int)cudaGetLastError();
 }
 
