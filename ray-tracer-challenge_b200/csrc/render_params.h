@@ -167,6 +167,9 @@ int launch_resolve(const ResolveParams& R, cudaStream_t stream);
 int launch_tile_order(const unsigned* cost, const unsigned long long* sum, unsigned* scratch, unsigned* order, unsigned n_tiles,
                       int last_bucket, int set, cudaStream_t stream);
 // ... or for frames streamed to a host canvas: bands of rows, cheapest band first, every tile started ahead of its row by what it costs
+// ... or for frames shared tile by tile: by cost in steps of 1/8 of the mean (heavy: six counters, cost >= 12x .. 2x the mean)
+int launch_fine_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned* heavy, unsigned n_tiles,
+                      void* temp, size_t temp_bytes, cudaStream_t stream);
 size_t row_order_temp_bytes(unsigned n_tiles);
 size_t row_order_work_words(unsigned n_tiles, unsigned tiles_x);
 int launch_row_order(const unsigned* cost, const unsigned long long* sum, unsigned* work, unsigned* order, unsigned n_tiles, unsigned tiles_x,

@@ -985,23 +985,36 @@ static int enqueue_frame(rtc_scene* s, const rtc_camera* cam, int max_depth, con
                 view.by_work = forced_seq >= 0 ? (forced_seq != 0) : !(s->best_ms[0] > 0.0f && link_ms > 1.4 * s->best_ms[0]);
             }
         }
-        if (s->pending == n_tiles && s->pending_view.last_bucket < 0) {
-            if (s->row_work_cap < n_tiles) {
-                CUDA_TRY(cudaStreamSynchronize(stream));
-                if (s->d_row_work) cudaFree(s->d_row_work);
-                s->d_row_work = nullptr;
-                s->row_work_cap = 0;
-                s->row_temp_bytes = row_order_temp_bytes((unsigned)n_tiles);
-                CUDA_TRY(cudaMalloc(&s->d_row_work, (3 * n_tiles + 3 * (n_tiles + 8) + 8) * sizeof(unsigned) + 256 + s->row_temp_bytes));  // (rows <= tiles)
-                s->row_work_cap = n_tiles;
-            }
+        static const bool fine_dealt = [] {  // shared frames: the order by cost in eighths of the mean (tile_order.cu launch_fine_order)
+            const char* e = std::getenv("RTC_FINE_ORDER");
+            return !(e && e[0] == '0');
+        }();
+        const bool sorted_order = s->pending == n_tiles && (s->pending_view.last_bucket < 0 || (s->pending_view.bucket_set == 1 && fine_dealt));
+        if (sorted_order && s->row_work_cap < n_tiles) {  // keys, sorted keys, tile numbers, row tables; then cub's temporary storage
+            CUDA_TRY(cudaStreamSynchronize(stream));
+            if (s->d_row_work) cudaFree(s->d_row_work);
+            s->d_row_work = nullptr;
+            s->row_work_cap = 0;
+            s->row_temp_bytes = row_order_temp_bytes((unsigned)n_tiles);
+            CUDA_TRY(cudaMalloc(&s->d_row_work, (3 * n_tiles + 3 * (n_tiles + 8) + 8) * sizeof(unsigned) + 256 + s->row_temp_bytes));  // (rows <= tiles)
+            s->row_work_cap = n_tiles;
+        }
+        void* const sort_temp = s->d_row_work ? reinterpret_cast<char*>(s->d_row_work) + (((3 * s->row_work_cap + 3 * (s->row_work_cap + 8) + 8) * sizeof(unsigned) + 255) & ~size_t(255)) : nullptr;
+        if (sorted_order && s->pending_view.last_bucket >= 0) {
+            CUDA_TRY((cudaError_t)launch_fine_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2), s->d_row_work,
+                                                    s->d_tile_order, s->d_scratch + RTC_ORDER_BUCKETS * ((n_tiles + 1023) / 1024), (unsigned)n_tiles,
+                                                    sort_temp, s->row_temp_bytes, stream));
+            s->order_tiles = n_tiles;
+            s->order_view = s->pending_view;
+            F.order_made = true;
+        } else if (sorted_order) {
             static const unsigned lead_pct = [] {  // how far ahead, in per cent of the estimate (warps of the grid working side by side)
                 const char* e = std::getenv("RTC_ROW_LEAD");
                 int v = e ? std::atoi(e) : 100;
                 return (unsigned)(v >= 0 && v <= 1000 ? v : 100);
             }();
             const unsigned lead = (unsigned)((unsigned long long)s->grid * (RTC_BLOCK_THREADS / 32) * lead_pct / 100u);
-            void* temp = reinterpret_cast<char*>(s->d_row_work) + (((3 * s->row_work_cap + 3 * (s->row_work_cap + 8) + 8) * sizeof(unsigned) + 255) & ~size_t(255));
+            void* temp = sort_temp;
             CUDA_TRY((cudaError_t)launch_row_order(mine_prev, reinterpret_cast<const unsigned long long*>(mine_prev + cost_words(n_tiles) - 2),
                                                    s->d_row_work, s->d_tile_order, (unsigned)n_tiles, P.tiles_x, (unsigned)-s->pending_view.last_bucket, s->pending_view.by_work, lead,
                                                    temp, s->row_temp_bytes, stream));
