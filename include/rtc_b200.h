@@ -88,9 +88,10 @@ void rtc_scene_destroy(rtc_scene* scene);
 int rtc_render(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                double* rgb_out, rtc_stats* stats);
 /* Page-locked, device-mapped host memory for canvases.  rtc_render / rtc_render_rgba8 accept any host
- * pointer; when it comes from rtc_host_alloc (or is otherwise pinned and mapped) rtc_render lets the
- * kernel write the pixels straight into it over PCIe while it is still rendering, instead of staging the
- * frame in device memory and copying it afterwards.  The Zig shim allocates its staging canvas here. */
+ * pointer; when it comes from rtc_host_alloc (or is otherwise pinned and mapped) the frame reaches it WHILE it is
+ * still rendering -- whole frames: the kernel announces every finished row of tiles and the calling thread hands
+ * them to the copy engine; row partitions: warps of the kernel move them -- instead of being staged in device
+ * memory and copied afterwards (Output).  The Zig shim allocates its staging canvas here. */
 void* rtc_host_alloc(size_t nbytes);
 void rtc_host_free(void* p);
 /* lib.zig:135-155 twin: clamp()-quantised RGBA8 (color.zig:61-71), alpha 255, 4 bytes per pixel. */
