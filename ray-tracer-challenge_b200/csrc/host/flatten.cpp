@@ -63,11 +63,11 @@ struct Builder {
             rec.format = RTC_IMG_RGBA8;
             size_t at = texels.size();
             texels.resize(at + px * 4);
+            const uint8_t* src = im->rgb8.data();
+            uint8_t* dst = texels.data() + at;  // (16-byte aligned offset of a vector's storage: whole words)
             for (size_t i = 0; i < px; i++) {
-                texels[at + i * 4 + 0] = im->rgb8[i * 3 + 0];
-                texels[at + i * 4 + 1] = im->rgb8[i * 3 + 1];
-                texels[at + i * 4 + 2] = im->rgb8[i * 3 + 2];
-                texels[at + i * 4 + 3] = 255;
+                const uint32_t v = (uint32_t)src[i * 3] | ((uint32_t)src[i * 3 + 1] << 8) | ((uint32_t)src[i * 3 + 2] << 16) | 0xff000000u;
+                std::memcpy(dst + i * 4, &v, 4);
             }
         }
         int32_t id = (int32_t)images.size();
@@ -97,9 +97,23 @@ struct Builder {
         return (int32_t)uvs.size() - 1;
     }
 
+    // (the leaves of a mesh come one after the other with the same matrix and the same material: the last answer is
+    // kept, so that 140,940 triangles do not mean 281,880 heap-allocated keys and map look-ups)
+    rtc_transform last_transform{};
+    int32_t last_transform_id = -1;
+    Material last_material;
+    int32_t last_material_id = -1;
+
     int32_t add_transform(const Mat4& inverse) {
         rtc_transform rec{};
         rows3(inverse, rec.inverse);
+        if (last_transform_id >= 0 && std::memcmp(rec.inverse, last_transform.inverse, sizeof rec.inverse) == 0) return last_transform_id;
+        const int32_t found = find_transform(rec);
+        last_transform = rec;
+        last_transform_id = found;
+        return found;
+    }
+    int32_t find_transform(const rtc_transform& rec) {
         std::vector<uint64_t> key(12);
         for (int i = 0; i < 12; i++) key[i] = bits(rec.inverse[i]);
         auto it = transform_ids.find(key);
@@ -111,6 +125,17 @@ struct Builder {
     }
 
     int32_t add_material(const Material& m) {
+        if (last_material_id >= 0 && m.pattern.get() == last_material.pattern.get() && bits(m.ambient) == bits(last_material.ambient) &&
+            bits(m.diffuse) == bits(last_material.diffuse) && bits(m.specular) == bits(last_material.specular) &&
+            bits(m.shininess) == bits(last_material.shininess) && bits(m.reflective) == bits(last_material.reflective) &&
+            bits(m.transparency) == bits(last_material.transparency) && bits(m.refractive_index) == bits(last_material.refractive_index))
+            return last_material_id;
+        const int32_t found = find_material(m);
+        last_material = m;
+        last_material_id = found;
+        return found;
+    }
+    int32_t find_material(const Material& m) {
         int32_t pat = add_pattern(m.pattern);
         std::vector<uint64_t> key = {bits(m.ambient),      bits(m.diffuse),      bits(m.specular),
                                      bits(m.shininess),    bits(m.reflective),   bits(m.transparency),
@@ -379,6 +404,13 @@ std::vector<uint8_t> flatten_world(const World& world) {
     }
     Walker w{b};
     g_extent.clear();
+    {   // how many leaves there will be (the extents are wanted anyway and are kept): no regrowing of 100,000-record vectors
+        size_t n_leaves = 0;
+        for (const Shape& s : world.objects) n_leaves += extent_of(s).leaves;
+        b.leaves.reserve(n_leaves);
+        b.triangles.reserve(n_leaves);
+        b.normals.reserve(n_leaves);
+    }
     for (const Shape& s : world.objects) w.walk(s);
     g_extent.clear();
 
@@ -399,7 +431,13 @@ std::vector<uint8_t> flatten_world(const World& world) {
     h.n_csg_roots = (uint32_t)b.csg_roots.size();
     h.texel_bytes = b.texels.size();
 
-    std::vector<uint8_t> out(sizeof(rtc_blob_header));
+    std::vector<uint8_t> out;
+    out.reserve(sizeof(rtc_blob_header) + 16 * 16 + b.lights.size() * sizeof(rtc_light) + b.materials.size() * sizeof(rtc_material) +
+                b.patterns.size() * sizeof(rtc_pattern) + b.uvs.size() * sizeof(rtc_uv_pattern) + b.images.size() * sizeof(rtc_image) +
+                b.transforms.size() * sizeof(rtc_transform) + b.leaves.size() * sizeof(rtc_leaf) + b.triangles.size() * sizeof(rtc_triangle) +
+                b.normals.size() * sizeof(rtc_tri_normals) + b.guards.size() * sizeof(rtc_guard) + b.nodes.size() * sizeof(rtc_node) +
+                b.children.size() * sizeof(int32_t) + b.csg_roots.size() * sizeof(int32_t) + b.texels.size());
+    out.resize(sizeof(rtc_blob_header));
     h.off_lights = put(out, b.lights);
     h.off_materials = put(out, b.materials);
     h.off_patterns = put(out, b.patterns);
