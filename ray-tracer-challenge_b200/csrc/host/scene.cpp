@@ -222,6 +222,8 @@ std::unique_ptr<DivPlan> plan_divide(const std::vector<BBox>& pb, std::vector<ui
     BBox lb, rb;
     box.split(lb, rb);
     std::vector<uint32_t> l, r;
+    l.reserve(members.size());
+    r.reserve(members.size());
     for (uint32_t i : members) {
         if (lb.contains_box(pb[i])) l.push_back(i);
         else if (rb.contains_box(pb[i])) r.push_back(i);
