@@ -113,7 +113,8 @@ int rtc_render_device_frame(rtc_scene* scene, const rtc_camera* cam, int max_dep
  * 64-byte copy of the ray counters), nothing is synchronised and no statistics are returned.  rtc_stats_fetch waits for
  * the frames enqueued so far and hands out their statistics, oldest first (stats_out may be NULL to just drain; at most
  * 16 frames are kept -- older ones are dropped); it returns the first error any of those frames raised.  The first
- * four to six frames of a (scene, frame size) are measured to pick the kernel and therefore complete before the call
+ * frames of a (scene, frame size) are measured to pick the kernel -- five, eleven for small partitions, fifteen for
+ * frames shared tile by tile (six heavy-tile thresholds, two frames each) -- and therefore complete before the call
  * returns.  Frames of one scene are ordered among themselves even when put on different streams. */
 int rtc_render_device_async(rtc_scene* scene, const rtc_camera* cam, int max_depth, const rtc_partition* part,
                             double* d_frame, void* stream);
